@@ -1,0 +1,627 @@
+// Fused image->voxel back-projection for B200 (sm_100a).
+//
+// One launch replaces, for a whole batch of scenes, what the reference does
+// with ~40 ATen launches and a Python loop per scene
+// (mmdet3d/models/detectors/imvoxelnet.py:57-78 and 145-160): project every
+// voxel through every view, round to a pixel, test validity, gather the
+// C-channel feature of that pixel and reduce over the views.
+//
+// Work decomposition (both kernels):
+//   * a warp owns a tile of T consecutive voxels of one scene;
+//   * phase 1 -- all 32 lanes project (voxel, view) pairs of the tile and
+//     leave, per voxel, one int32 per view in a shared-memory table: the
+//     offset of the hit pixel, or -1.  The 3x4 matrices sit in shared memory,
+//     voxel coordinates are rebuilt in registers from the grid description;
+//   * phase 2 -- G lanes own one voxel: they compact the table row with a
+//     ballot, then stream the C contiguous channels of each hit pixel with
+//     128-bit loads (several pixels in flight), accumulating sum and count in
+//     registers; the epilogue divides, zeroes unseen voxels and stores.
+//
+// Bit-exactness of the pixel index (checked against the reference's outputs):
+// the K=4 dot product is evaluated as rn(P0*x) then three fma's -- what the
+// reference's torch.bmm (:150) does on CPU -- followed by IEEE division and
+// round-half-even.  Every float op on that path is an explicit _rn intrinsic
+// so that nvcc can neither contract nor reassociate it.
+#include <cuda_bf16.h>
+
+#include "ivx_common.cuh"
+
+namespace ivx {
+
+struct BpArgs {
+    const float *feat;
+    long long fs_b, fs_v, fs_c, fs_h, fs_w;  // element strides of [B][V][C][H][W]
+    const float *proj;                       // [B][V][12]
+    long long proj_stride_b;                 // elements between scenes' matrix blocks
+    const float *points;                     // [3][N] or nullptr
+    float vs[3];
+    int V, C, X, Y, Z, N;
+    void *vol;
+    long long os_b, os_c, os_n;
+    uint8_t *valid;  // [B][N]
+    int32_t *count;  // [B][N]
+    int reduce;      // ivx_reduce
+    int tile_log2;   // T = 1 << tile_log2, 2..5
+    int table_stride;
+    int hw[IVX_MAX_SCENES_PER_LAUNCH][2];
+    float new_origin[IVX_MAX_SCENES_PER_LAUNCH][3];
+};
+
+__device__ __forceinline__ float dot4_rn(const float *P, float x, float y, float z) {
+    float acc = __fmul_rn(P[0], x);
+    acc = __fmaf_rn(P[1], y, acc);
+    acc = __fmaf_rn(P[2], z, acc);
+    return __fadd_rn(acc, P[3]);  // fma(P3, 1, acc) == rn(acc + P3)
+}
+
+// Pixel hit by one voxel in one view.  Returns validity; xr/yr are the rounded
+// pixel coordinates as floats (exact integers when valid).
+__device__ __forceinline__ bool project_rn(const float *P, float px, float py, float pz,
+                                           int h, int w, float &xr, float &yr) {
+    const float p0 = dot4_rn(P, px, py, pz);
+    const float p1 = dot4_rn(P + 4, px, py, pz);
+    const float p2 = dot4_rn(P + 8, px, py, pz);
+    xr = rintf(__fdiv_rn(p0, p2));
+    yr = rintf(__fdiv_rn(p1, p2));
+    // -0.0f >= 0 holds (pixel 0); NaN / inf compare false, like the reference's
+    // cast-then-compare on every platform.
+    return (xr >= 0.0f) & (yr >= 0.0f) & (xr < (float)w) & (yr < (float)h) & (p2 > 0.0f);
+}
+
+__device__ __forceinline__ void voxel_coords(const BpArgs &a, int b, int n, float &px,
+                                             float &py, float &pz) {
+    if (a.points != nullptr) {
+        px = __ldg(a.points + n);
+        py = __ldg(a.points + a.N + n);
+        pz = __ldg(a.points + 2ll * a.N + n);
+    } else {
+        const int iz = n % a.Z;
+        const int t = n / a.Z;
+        const int iy = t % a.Y;
+        const int ix = t / a.Y;
+        px = __fadd_rn(__fmul_rn((float)ix, a.vs[0]), a.new_origin[b][0]);
+        py = __fadd_rn(__fmul_rn((float)iy, a.vs[1]), a.new_origin[b][1]);
+        pz = __fadd_rn(__fmul_rn((float)iz, a.vs[2]), a.new_origin[b][2]);
+    }
+}
+
+// Phase 1.  table[j * stride + v] = offset of the pixel voxel j hits in view v
+// (in units of `1 << OFF_SHIFT` elements), or -1.
+template <int OFF_SHIFT>
+__device__ __forceinline__ void fill_table(const BpArgs &a, const float *sP, int *table, int b,
+                                           int n0, int lane) {
+    const int T = 1 << a.tile_log2;
+    const int j = lane & (T - 1);
+    const int vq = lane >> a.tile_log2;
+    const int vstep = 32 >> a.tile_log2;
+    const int n = n0 + j;
+    if (n < a.N) {
+        float px, py, pz;
+        voxel_coords(a, b, n, px, py, pz);
+        const int h = a.hw[b][0], w = a.hw[b][1];
+        for (int v = vq; v < a.V; v += vstep) {
+            float xr, yr;
+            const bool ok = project_rn(sP + 12 * v, px, py, pz, h, w, xr, yr);
+            long long off = -1;
+            if (ok) off = (v * a.fs_v + (long long)yr * a.fs_h + (long long)xr * a.fs_w) >> OFF_SHIFT;
+            table[j * a.table_stride + v] = (int)off;
+        }
+    }
+    __syncwarp();
+}
+
+template <typename OutT>
+__device__ __forceinline__ void store4(OutT *p, float4 v);
+
+template <>
+__device__ __forceinline__ void store4<float>(float *p, float4 v) {
+    __stcs(reinterpret_cast<float4 *>(p), v);
+}
+
+template <>
+__device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16 *p, float4 v) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 u;
+    u.x = *reinterpret_cast<unsigned *>(&lo);
+    u.y = *reinterpret_cast<unsigned *>(&hi);
+    __stcs(reinterpret_cast<uint2 *>(p), u);
+}
+
+// ---------------------------------------------------------------------------
+// Vectorised kernel: channels-last features (fs_c == 1), channels-last volume
+// (os_c == 1).  G lanes per voxel, CPL float4 per lane; G * CPL * 4 >= C.
+// ---------------------------------------------------------------------------
+template <int G, int CPL, typename OutT>
+__global__ void __launch_bounds__(256) bp_vec_kernel(const __grid_constant__ BpArgs a) {
+    extern __shared__ int smem[];
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int UNROLL = (CPL >= 4) ? 2 : 4;  // pixels in flight per voxel
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    const int T = 1 << a.tile_log2;
+
+    float *sP = reinterpret_cast<float *>(smem);
+    for (int i = threadIdx.x; i < a.V * 12; i += blockDim.x)
+        sP[i] = __ldg(a.proj + b * a.proj_stride_b + i);
+    __syncthreads();
+    int *table = smem + ((a.V * 12 + 3) & ~3) + warp * T * a.table_stride;
+
+    const float4 *feat4 = reinterpret_cast<const float4 *>(a.feat + b * a.fs_b);
+    OutT *vol = reinterpret_cast<OutT *>(a.vol) + b * a.os_b;
+    const int g = lane / G;
+    const int t = lane % G;
+    const int ntiles = (a.N + T - 1) >> a.tile_log2;
+
+    bool ch_ok[CPL];
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) ch_ok[i] = (t + i * G) * 4 < a.C;
+
+    for (int tile = blockIdx.x * nwarps + warp; tile < ntiles; tile += gridDim.x * nwarps) {
+        const int n0 = tile << a.tile_log2;
+        fill_table<2>(a, sP, table, b, n0, lane);
+
+        for (int j0 = 0; j0 < T; j0 += 32 / G) {
+            const int j = j0 + g;
+            const int n = n0 + j;
+            const bool active = (j < T) && (n < a.N);
+            float4 acc[CPL];
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            int cnt = 0;
+
+            for (int c0 = 0; c0 < a.V; c0 += G) {
+                const int v = c0 + t;
+                const int off = (active && v < a.V) ? table[j * a.table_stride + v] : -1;
+                const unsigned m = __ballot_sync(FULL, off >= 0);
+                unsigned gm = (G == 32) ? m : ((m >> (g * G)) & ((1u << (G & 31)) - 1u));
+                cnt += __popc(gm);
+                while (__any_sync(FULL, gm != 0)) {
+                    int o[UNROLL];
+#pragma unroll
+                    for (int u = 0; u < UNROLL; ++u) {
+                        const bool has = gm != 0;
+                        const int src = has ? (__ffs(gm) - 1) : 0;
+                        gm &= gm - 1;  // 0 stays 0
+                        const int ov = __shfl_sync(FULL, off, src, G);
+                        o[u] = has ? ov : -1;
+                    }
+                    float4 r[UNROLL][CPL];
+#pragma unroll
+                    for (int u = 0; u < UNROLL; ++u)
+#pragma unroll
+                        for (int i = 0; i < CPL; ++i) {
+                            r[u][i] = make_float4(0.f, 0.f, 0.f, 0.f);
+                            if (o[u] >= 0 && ch_ok[i]) r[u][i] = __ldg(feat4 + o[u] + t + i * G);
+                        }
+#pragma unroll
+                    for (int u = 0; u < UNROLL; ++u)  // ascending view order
+#pragma unroll
+                        for (int i = 0; i < CPL; ++i) {
+                            acc[i].x += r[u][i].x;
+                            acc[i].y += r[u][i].y;
+                            acc[i].z += r[u][i].z;
+                            acc[i].w += r[u][i].w;
+                        }
+                }
+            }
+
+            if (active) {
+                if (a.reduce == IVX_REDUCE_MEAN) {
+                    // sum / count (count converted to float, :72); 0 where unseen (:74)
+                    const float c = (float)cnt;
+#pragma unroll
+                    for (int i = 0; i < CPL; ++i) {
+                        acc[i].x = cnt ? __fdiv_rn(acc[i].x, c) : 0.f;
+                        acc[i].y = cnt ? __fdiv_rn(acc[i].y, c) : 0.f;
+                        acc[i].z = cnt ? __fdiv_rn(acc[i].z, c) : 0.f;
+                        acc[i].w = cnt ? __fdiv_rn(acc[i].w, c) : 0.f;
+                    }
+                }
+                OutT *dst = vol + (long long)n * a.os_n;
+#pragma unroll
+                for (int i = 0; i < CPL; ++i)
+                    if (ch_ok[i]) store4<OutT>(dst + (t + i * G) * 4, acc[i]);
+                if (t == 0) {
+                    if (a.valid) a.valid[(long long)b * a.N + n] = cnt > 0;
+                    if (a.count) a.count[(long long)b * a.N + n] = cnt;
+                }
+            }
+        }
+        __syncwarp();  // table is rewritten by the next tile
+    }
+}
+
+// ---------------------------------------------------------------------------
+// Strided kernel: any feature strides (the reference's NCHW slice, :69), any
+// channel count, any fp32 volume strides.  Lanes own channels.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) bp_strided_kernel(const __grid_constant__ BpArgs a) {
+    extern __shared__ int smem[];
+    constexpr unsigned FULL = 0xffffffffu;
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    const int T = 1 << a.tile_log2;
+
+    float *sP = reinterpret_cast<float *>(smem);
+    for (int i = threadIdx.x; i < a.V * 12; i += blockDim.x)
+        sP[i] = __ldg(a.proj + b * a.proj_stride_b + i);
+    __syncthreads();
+    int *table = smem + ((a.V * 12 + 3) & ~3) + warp * T * a.table_stride;
+
+    const float *feat = a.feat + b * a.fs_b;
+    float *vol = reinterpret_cast<float *>(a.vol) + b * a.os_b;
+    const int ntiles = (a.N + T - 1) >> a.tile_log2;
+
+    for (int tile = blockIdx.x * nwarps + warp; tile < ntiles; tile += gridDim.x * nwarps) {
+        const int n0 = tile << a.tile_log2;
+        fill_table<0>(a, sP, table, b, n0, lane);
+        for (int j = 0; j < T; ++j) {
+            const int n = n0 + j;
+            if (n >= a.N) break;
+            const int *row = table + j * a.table_stride;
+            int cnt = 0;
+            for (int c0 = 0; c0 < a.V; c0 += 32) {
+                const int v = c0 + lane;
+                const int off = v < a.V ? row[v] : -1;
+                cnt += __popc(__ballot_sync(FULL, off >= 0));
+            }
+            const float fc = (float)cnt;
+            for (int cb = 0; cb < a.C; cb += 32) {
+                const int c = cb + lane;
+                if (c < a.C) {
+                    float acc = 0.f;
+                    for (int v = 0; v < a.V; ++v) {
+                        const int off = row[v];
+                        if (off >= 0) acc += __ldg(feat + off + c * a.fs_c);
+                    }
+                    if (a.reduce == IVX_REDUCE_MEAN) acc = cnt ? __fdiv_rn(acc, fc) : 0.f;
+                    vol[c * a.os_c + (long long)n * a.os_n] = acc;
+                }
+            }
+            if (lane == 0) {
+                if (a.valid) a.valid[(long long)b * a.N + n] = cnt > 0;
+                if (a.count) a.count[(long long)b * a.N + n] = cnt;
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// x, y, valid of every voxel-view (the reference's locals at :151-154).
+__global__ void __launch_bounds__(256) project_indices_kernel(
+    const float *__restrict__ points, ivx_grid grid, float nox, float noy, float noz, int N,
+    const float *__restrict__ proj, int V, int h, int w, int32_t *__restrict__ x,
+    int32_t *__restrict__ y, uint8_t *__restrict__ valid) {
+    const int v = blockIdx.y;
+    __shared__ float P[12];
+    if (threadIdx.x < 12) P[threadIdx.x] = proj[v * 12 + threadIdx.x];
+    __syncthreads();
+    for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x) {
+        float px, py, pz;
+        if (points != nullptr) {
+            px = points[n];
+            py = points[N + n];
+            pz = points[2ll * N + n];
+        } else {
+            const int iz = n % grid.n_voxels[2];
+            const int t = n / grid.n_voxels[2];
+            const int iy = t % grid.n_voxels[1];
+            const int ix = t / grid.n_voxels[1];
+            px = __fadd_rn(__fmul_rn((float)ix, grid.voxel_size[0]), nox);
+            py = __fadd_rn(__fmul_rn((float)iy, grid.voxel_size[1]), noy);
+            pz = __fadd_rn(__fmul_rn((float)iz, grid.voxel_size[2]), noz);
+        }
+        float xr, yr;
+        const bool ok = project_rn(P, px, py, pz, h, w, xr, yr);
+        const long long o = (long long)v * N + n;
+        if (x) x[o] = ok ? (int)xr : INT32_MIN;
+        if (y) y[o] = ok ? (int)yr : INT32_MIN;
+        valid[o] = ok;
+    }
+}
+
+__global__ void __launch_bounds__(256) finalize_mean_kernel(
+    const float4 *__restrict__ sum, const int32_t *__restrict__ count, long long n_rows, int c4,
+    int N, void *vol, long long os_b, long long os_c, long long os_n, int dtype,
+    uint8_t *__restrict__ valid) {
+    const long long total = n_rows * c4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / c4;
+        const int q = (int)(i - row * c4);
+        const int cnt = __ldg(count + row);
+        float4 s = __ldcs(sum + i);
+        const float c = (float)cnt;
+        s.x = cnt ? __fdiv_rn(s.x, c) : 0.f;
+        s.y = cnt ? __fdiv_rn(s.y, c) : 0.f;
+        s.z = cnt ? __fdiv_rn(s.z, c) : 0.f;
+        s.w = cnt ? __fdiv_rn(s.w, c) : 0.f;
+        const long long b = row / N, n = row - b * N;
+        const long long base = b * os_b + n * os_n;
+        if (os_c == 1) {
+            if (dtype == IVX_F32)
+                store4<float>(reinterpret_cast<float *>(vol) + base + q * 4, s);
+            else
+                store4<__nv_bfloat16>(reinterpret_cast<__nv_bfloat16 *>(vol) + base + q * 4, s);
+        } else {
+            float *o = reinterpret_cast<float *>(vol) + base + (long long)q * 4 * os_c;
+            o[0] = s.x;
+            o[os_c] = s.y;
+            o[2 * os_c] = s.z;
+            o[3 * os_c] = s.w;
+        }
+        if (q == 0 && valid) valid[row] = cnt > 0;
+    }
+}
+
+// NCHW -> NHWC through a 32x33 shared-memory tile, coalesced on both sides.
+__global__ void __launch_bounds__(256) repack_nchw_nhwc_kernel(
+    const float *__restrict__ src, long long s_i, long long s_c, long long s_h, long long s_w,
+    int C, int H, int W, float *__restrict__ dst) {
+    __shared__ float tile[32][33];
+    const int img = blockIdx.z;
+    const int HW = H * W;
+    const int p0 = blockIdx.x * 32;  // pixel tile
+    const int c0 = blockIdx.y * 32;  // channel tile
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;  // 32 x 8
+    for (int r = ty; r < 32; r += 8) {
+        const int c = c0 + r, p = p0 + tx;
+        float v = 0.f;
+        if (c < C && p < HW) {
+            const int yy = p / W, xx = p - yy * W;
+            v = __ldcs(src + img * s_i + c * s_c + yy * s_h + xx * s_w);
+        }
+        tile[r][tx] = v;
+    }
+    __syncthreads();
+    for (int r = ty; r < 32; r += 8) {
+        const int p = p0 + r, c = c0 + tx;
+        if (c < C && p < HW) dst[((long long)img * HW + p) * C + c] = tile[tx][r];
+    }
+}
+
+// ------------------------------- host side --------------------------------
+
+static int pick_tile_log2(long long n_points, int n_scenes) {
+    // largest tile that still gives every SM ~32 warps of work
+    for (int lg = 5; lg > 2; --lg) {
+        const long long tiles = ((n_points + (1 << lg) - 1) >> lg) * n_scenes;
+        if (tiles >= (long long)kNumSMs * 32) return lg;
+    }
+    return 2;
+}
+
+template <typename OutT>
+static void *pick_vec_kernel(int C) {
+    const int c4 = (C + 3) / 4;
+    if (c4 <= 8) return (void *)bp_vec_kernel<8, 1, OutT>;
+    if (c4 <= 16) return (void *)bp_vec_kernel<16, 1, OutT>;
+    if (c4 <= 32) return (void *)bp_vec_kernel<32, 1, OutT>;
+    if (c4 <= 64) return (void *)bp_vec_kernel<32, 2, OutT>;
+    if (c4 <= 128) return (void *)bp_vec_kernel<32, 4, OutT>;
+    if (c4 <= 256) return (void *)bp_vec_kernel<32, 8, OutT>;
+    return nullptr;
+}
+
+static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// One launch over at most IVX_MAX_SCENES_PER_LAUNCH scenes.
+static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t stream) {
+    const bool feat_vec = a.fs_c == 1 && a.C % 4 == 0 && aligned16(a.feat) && a.fs_b % 4 == 0 &&
+                          a.fs_v % 4 == 0 && a.fs_h % 4 == 0 && a.fs_w % 4 == 0;
+    const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
+    const bool vol_vec = a.os_c == 1 && a.os_b % 4 == 0 && a.os_n % 4 == 0 &&
+                         (reinterpret_cast<uintptr_t>(a.vol) % (4 * esz)) == 0;
+    void *kernel = nullptr;
+    if (feat_vec && vol_vec)
+        kernel = vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16>(a.C) : pick_vec_kernel<float>(a.C);
+    if (kernel == nullptr) {
+        if (vol_dtype != IVX_F32)
+            return fail(IVX_ERR_UNSUPPORTED,
+                        "bf16 volumes need channels-last features and volume (C %% 4 == 0, C <= 1024)");
+        kernel = (void *)bp_strided_kernel;
+        // table entries are int32 element offsets inside one scene's block
+        const long long span = llabs(a.fs_v) * a.V + llabs(a.fs_c) * a.C;
+        long long hmax = 0, wmax = 0;
+        for (int b = 0; b < n_scenes; ++b) {
+            hmax = a.hw[b][0] > hmax ? a.hw[b][0] : hmax;
+            wmax = a.hw[b][1] > wmax ? a.hw[b][1] : wmax;
+        }
+        if (span + llabs(a.fs_h) * hmax + llabs(a.fs_w) * wmax >= (1ll << 31))
+            return fail(IVX_ERR_UNSUPPORTED, "feature block of one scene exceeds 2^31 elements");
+    }
+
+    a.tile_log2 = pick_tile_log2(a.N, n_scenes);
+    a.table_stride = a.V | 1;
+    const int T = 1 << a.tile_log2;
+    const size_t proj_words = (a.V * 12 + 3) & ~3;
+    int warps = 8;
+    size_t smem = 0;
+    for (;; warps >>= 1) {
+        smem = (proj_words + (size_t)warps * T * a.table_stride) * sizeof(int);
+        if (smem <= 96 * 1024 || warps == 1) break;
+    }
+    if (smem > 200 * 1024) return fail(IVX_ERR_UNSUPPORTED, "too many views for one tile table");
+    if (smem > 48 * 1024) {
+        int rc = check_cuda(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                 (int)smem),
+                            "cudaFuncSetAttribute");
+        if (rc != IVX_OK) return rc;
+    }
+    const long long ntiles = ((long long)a.N + T - 1) >> a.tile_log2;
+    long long gx = (ntiles + warps - 1) / warps;
+    if (gx > 65535ll * 16) gx = 65535ll * 16;  // grid-stride loop covers the rest
+    dim3 grid((unsigned)gx, (unsigned)n_scenes, 1), block(warps * 32, 1, 1);
+    void *params[] = {&a};
+    int rc = check_cuda(cudaLaunchKernel(kernel, grid, block, params, smem, stream), "backproject launch");
+    return rc;
+}
+
+static int validate_grid(const float *points, const ivx_grid *grid, const float *new_origin,
+                         int64_t n_points) {
+    IVX_REQUIRE(n_points > 0 && n_points < (1ll << 31), "n_points must be in [1, 2^31)");
+    if (points == nullptr) {
+        IVX_REQUIRE(grid != nullptr && new_origin != nullptr,
+                    "either points or grid + new_origin must be given");
+        const long long n = (long long)grid->n_voxels[0] * grid->n_voxels[1] * grid->n_voxels[2];
+        IVX_REQUIRE(grid->n_voxels[0] > 0 && grid->n_voxels[1] > 0 && grid->n_voxels[2] > 0 &&
+                        n == n_points,
+                    "grid %dx%dx%d does not hold n_points=%lld", grid->n_voxels[0],
+                    grid->n_voxels[1], grid->n_voxels[2], (long long)n_points);
+    }
+    return IVX_OK;
+}
+
+static int backproject_batch(const float *feat, const long long fs[5], int B, int V, int C,
+                             const int32_t *hw, bool hw_per_scene, const float *proj,
+                             long long proj_stride_b, const float *points, const ivx_grid *grid,
+                             const float *new_origin, bool origin_per_scene, int64_t N, void *volume,
+                             const int64_t *vs, int vol_dtype, int reduce, uint8_t *valid,
+                             int32_t *count, cudaStream_t stream) {
+    const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
+    for (int b0 = 0; b0 < B; b0 += IVX_MAX_SCENES_PER_LAUNCH) {
+        const int nb = (B - b0 < IVX_MAX_SCENES_PER_LAUNCH) ? B - b0 : IVX_MAX_SCENES_PER_LAUNCH;
+        BpArgs a;
+        a.feat = feat + b0 * fs[0];
+        a.fs_b = fs[0], a.fs_v = fs[1], a.fs_c = fs[2], a.fs_h = fs[3], a.fs_w = fs[4];
+        a.proj = proj + b0 * proj_stride_b;
+        a.proj_stride_b = proj_stride_b;
+        a.points = points;
+        a.V = V, a.C = C, a.N = (int)N;
+        a.X = a.Y = a.Z = 1;
+        a.vs[0] = a.vs[1] = a.vs[2] = 0.f;
+        if (points == nullptr) {
+            a.X = grid->n_voxels[0], a.Y = grid->n_voxels[1], a.Z = grid->n_voxels[2];
+            for (int k = 0; k < 3; ++k) a.vs[k] = grid->voxel_size[k];
+        }
+        a.vol = static_cast<char *>(volume) + (size_t)(b0 * vs[0]) * esz;
+        a.os_b = vs[0], a.os_c = vs[1], a.os_n = vs[2];
+        a.valid = valid ? valid + (long long)b0 * N : nullptr;
+        a.count = count ? count + (long long)b0 * N : nullptr;
+        a.reduce = reduce;
+        for (int b = 0; b < nb; ++b) {
+            const int32_t *p = hw + (hw_per_scene ? 2 * (b0 + b) : 0);
+            a.hw[b][0] = p[0], a.hw[b][1] = p[1];
+            for (int k = 0; k < 3; ++k)
+                a.new_origin[b][k] =
+                    new_origin ? new_origin[(origin_per_scene ? 3 * (b0 + b) : 0) + k] : 0.f;
+        }
+        int rc = launch_scenes(a, nb, vol_dtype, stream);
+        if (rc != IVX_OK) return rc;
+    }
+    return IVX_OK;
+}
+
+}  // namespace ivx
+
+using namespace ivx;
+
+extern "C" int ivx_project_indices(const float *points, const ivx_grid *grid, const float *new_origin,
+                                   int64_t n_points, const float *proj, int n_views, int height,
+                                   int width, int32_t *x, int32_t *y, uint8_t *valid, void *stream) {
+    int rc = validate_grid(points, grid, new_origin, n_points);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(proj != nullptr && valid != nullptr, "proj and valid must not be NULL");
+    IVX_REQUIRE(n_views > 0 && n_views <= 65535, "n_views out of range");
+    IVX_REQUIRE(height > 0 && width > 0, "height/width must be positive");
+    ivx_grid g = {{1, 1, 1}, {0.f, 0.f, 0.f}};
+    float no[3] = {0.f, 0.f, 0.f};
+    if (points == nullptr) {
+        g = *grid;
+        for (int k = 0; k < 3; ++k) no[k] = new_origin[k];
+    }
+    long long gx = (n_points + 255) / 256;
+    if (gx > kNumSMs * 64) gx = kNumSMs * 64;
+    project_indices_kernel<<<dim3((unsigned)gx, (unsigned)n_views), 256, 0, (cudaStream_t)stream>>>(
+        points, g, no[0], no[1], no[2], (int)n_points, proj, n_views, height, width, x, y, valid);
+    IVX_CHECK_LAUNCH("project_indices launch");
+    return IVX_OK;
+}
+
+extern "C" int ivx_backproject_scenes(const float *feat, const int64_t *feat_strides, int n_scenes,
+                                      int n_views, int n_channels, const int32_t *hw,
+                                      const float *proj, const float *points, const ivx_grid *grid,
+                                      const float *new_origin, int64_t n_points, void *volume,
+                                      const int64_t *vol_strides, int vol_dtype, int reduce,
+                                      uint8_t *valid, int32_t *count, void *stream) {
+    int rc = validate_grid(points, grid, new_origin, n_points);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(feat && feat_strides && hw && proj && volume && vol_strides, "NULL argument");
+    IVX_REQUIRE(n_scenes > 0 && n_channels > 0, "n_scenes and n_channels must be positive");
+    IVX_REQUIRE(n_views > 0 && n_views <= IVX_MAX_VIEWS, "n_views must be in [1, %d]", IVX_MAX_VIEWS);
+    IVX_REQUIRE(vol_dtype == IVX_F32 || vol_dtype == IVX_BF16, "unknown vol_dtype %d", vol_dtype);
+    IVX_REQUIRE(reduce == IVX_REDUCE_MEAN || reduce == IVX_REDUCE_PARTIAL, "unknown reduce %d", reduce);
+    if (reduce == IVX_REDUCE_PARTIAL)
+        IVX_REQUIRE(count != nullptr && vol_dtype == IVX_F32, "partial sums need count and fp32 volume");
+    for (int b = 0; b < n_scenes; ++b)
+        IVX_REQUIRE(hw[2 * b] > 0 && hw[2 * b + 1] > 0, "scene %d: height/width must be positive", b);
+    const long long fs[5] = {feat_strides[0], feat_strides[1], feat_strides[2], feat_strides[3],
+                             feat_strides[4]};
+    return backproject_batch(feat, fs, n_scenes, n_views, n_channels, hw, true, proj,
+                             12ll * n_views, points, grid, new_origin, true, n_points, volume,
+                             vol_strides, vol_dtype, reduce, valid, count, (cudaStream_t)stream);
+}
+
+extern "C" int ivx_backproject_views(const float *feat, const int64_t *feat_strides, int n_views,
+                                     int n_channels, int height, int width, const float *proj,
+                                     const float *points, const ivx_grid *grid,
+                                     const float *new_origin, int64_t n_points, float *volume,
+                                     const int64_t *vol_strides, uint8_t *valid, void *stream) {
+    int rc = validate_grid(points, grid, new_origin, n_points);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(feat && feat_strides && proj && volume && vol_strides && valid, "NULL argument");
+    IVX_REQUIRE(n_views > 0 && n_channels > 0 && height > 0 && width > 0, "sizes must be positive");
+    // every view is a one-view "scene": its sum is the gathered feature or 0
+    const long long fs[5] = {feat_strides[0], 0, feat_strides[1], feat_strides[2], feat_strides[3]};
+    const int32_t hw[2] = {height, width};
+    return backproject_batch(feat, fs, n_views, 1, n_channels, hw, false, proj, 12, points, grid,
+                             new_origin, false, n_points, volume, vol_strides, IVX_F32,
+                             IVX_REDUCE_PARTIAL, valid, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int ivx_finalize_mean(const float *sum, const int32_t *count, int n_scenes, int n_channels,
+                                 int64_t n_points, void *volume, const int64_t *vol_strides,
+                                 int vol_dtype, uint8_t *valid, void *stream) {
+    IVX_REQUIRE(sum && count && volume && vol_strides, "NULL argument");
+    IVX_REQUIRE(n_scenes > 0 && n_points > 0 && n_points < (1ll << 31), "sizes out of range");
+    IVX_REQUIRE(n_channels > 0 && n_channels % 4 == 0 && aligned16(sum),
+                "partial sums must be channels-last with C %% 4 == 0 and 16-byte aligned");
+    IVX_REQUIRE(vol_dtype == IVX_F32 || vol_dtype == IVX_BF16, "unknown vol_dtype %d", vol_dtype);
+    const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
+    if (vol_strides[1] == 1)
+        IVX_REQUIRE(vol_strides[0] % 4 == 0 && vol_strides[2] % 4 == 0 &&
+                        reinterpret_cast<uintptr_t>(volume) % (4 * esz) == 0,
+                    "channels-last volume must be aligned to 4 elements");
+    else
+        IVX_REQUIRE(vol_dtype == IVX_F32, "bf16 volumes must be channels-last");
+    const long long rows = (long long)n_scenes * n_points;
+    const int c4 = n_channels / 4;
+    long long gx = (rows * c4 + 255) / 256;
+    if (gx > kNumSMs * 32) gx = kNumSMs * 32;
+    finalize_mean_kernel<<<(unsigned)gx, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const float4 *>(sum), count, rows, c4, (int)n_points, volume, vol_strides[0],
+        vol_strides[1], vol_strides[2], vol_dtype, valid);
+    IVX_CHECK_LAUNCH("finalize_mean launch");
+    return IVX_OK;
+}
+
+extern "C" int ivx_repack_nchw_to_nhwc(const float *src, const int64_t *src_strides, int n_images,
+                                       int n_channels, int height, int width, float *dst,
+                                       void *stream) {
+    IVX_REQUIRE(src && src_strides && dst, "NULL argument");
+    IVX_REQUIRE(n_images > 0 && n_images <= 65535 && n_channels > 0 && height > 0 && width > 0,
+                "sizes out of range");
+    const long long hw = (long long)height * width;
+    IVX_REQUIRE(hw < (1ll << 31) && (n_channels + 31) / 32 <= 65535, "map too large");
+    dim3 grid((unsigned)((hw + 31) / 32), (unsigned)((n_channels + 31) / 32), (unsigned)n_images);
+    repack_nchw_nhwc_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+        src, src_strides[0], src_strides[1], src_strides[2], src_strides[3], n_channels, height,
+        width, dst);
+    IVX_CHECK_LAUNCH("repack launch");
+    return IVX_OK;
+}

@@ -1,0 +1,174 @@
+/*
+ * libivx -- B200 (sm_100a) kernels for ImVoxelNet's image->voxel path, C ABI.
+ *
+ * This is the drop-in boundary: plain pointers, sizes and a CUDA stream; no
+ * torch / C++ types.  The reference (SamsungLabs/imvoxelnet, a Python/PyTorch
+ * code base) has no FFI of its own for this path -- it runs ~40 ATen kernels
+ * per scene.  Each entry point below therefore cites the reference *Python*
+ * code it replaces; paths are relative to the reference tree.  The Python
+ * mirror that binds these symbols with ctypes is imvoxelnet_b200/_lib.py;
+ * INTEGRATION.md shows the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - Every data pointer is a DEVICE pointer on the current device unless the
+ *     parameter comment says "host".  The caller owns all memory; the library
+ *     never allocates or frees device memory and never synchronises.
+ *   - All work is enqueued on `stream` (a cudaStream_t passed as void*; NULL is
+ *     the legacy default stream).
+ *   - Return value: IVX_OK or a negative ivx_status; ivx_last_error() gives the
+ *     message of the last failure on the calling thread.  No C++ exception
+ *     crosses this boundary.
+ *   - Voxel linear index n = (ix*Y + iy)*Z + iz (Z fastest), as the reference's
+ *     meshgrid builds it (mmdet3d/models/detectors/imvoxelnet.py:134-138).
+ *   - Strides are in ELEMENTS, not bytes.
+ */
+#ifndef IVX_H_
+#define IVX_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* the library is built with -fvisibility=hidden: only these symbols are exported */
+#if defined(__GNUC__)
+#define IVX_API __attribute__((visibility("default")))
+#else
+#define IVX_API
+#endif
+
+typedef enum ivx_status {
+    IVX_OK = 0,
+    IVX_ERR_INVALID_ARGUMENT = -1,
+    IVX_ERR_UNSUPPORTED = -2,
+    IVX_ERR_CUDA = -3
+} ivx_status;
+
+/* element type of a volume written by the library */
+typedef enum ivx_dtype { IVX_F32 = 0, IVX_BF16 = 1 } ivx_dtype;
+
+/* what ivx_backproject_scenes writes */
+typedef enum ivx_reduce {
+    IVX_REDUCE_MEAN = 0,    /* sum / count, 0 where count == 0  (:70-74)          */
+    IVX_REDUCE_PARTIAL = 1  /* raw fp32 sum + int32 count (view-sharded multi-GPU) */
+} ivx_reduce;
+
+#define IVX_MAX_SCENES_PER_LAUNCH 64 /* larger batches are split internally */
+#define IVX_MAX_VIEWS 1024
+
+/* Library / build identification ("libivx 0.1 sm_100a ..."). Never NULL. */
+IVX_API const char *ivx_version(void);
+
+/* Message of the last error raised on this thread ("" if none). */
+IVX_API const char *ivx_last_error(void);
+
+/*
+ * Regular voxel grid, replaces get_points (detectors/imvoxelnet.py:132-141):
+ * coordinate of voxel (i,j,k) on axis a is  rn(rn(idx_a * voxel_size[a]) +
+ * new_origin[a]),  new_origin = origin - n_voxels/2 * voxel_size computed by
+ * the caller in fp32 (:139).  The kernels rebuild the coordinates in registers
+ * from this description, so no [3,N] tensor has to exist.
+ */
+typedef struct ivx_grid {
+    int32_t n_voxels[3];  /* X, Y, Z */
+    float voxel_size[3];
+} ivx_grid;
+
+/*
+ * ivx_project_indices -- pixel indices and valid mask of every voxel-view.
+ * Replaces the index arithmetic of backproject (detectors/imvoxelnet.py
+ * :148-154): homogeneous projection with the K=4 fma chain of torch.bmm,
+ * IEEE division, round-half-even, in-image & positive-depth test.
+ *
+ *   points      [3][N] fp32 voxel coordinates, or NULL to build them from
+ *               `grid` + `new_origin` (host, 3 floats)
+ *   proj        [V][12] fp32 row-major 3x4 matrices
+ *   x, y        [V][N] int32 out (either may be NULL).  On lanes where valid==0
+ *               the value is unspecified (the reference's own value there is
+ *               platform dependent: x86 and CUDA cast inf/NaN differently).
+ *   valid       [V][N] uint8 out (0/1)
+ */
+IVX_API int ivx_project_indices(const float *points, const ivx_grid *grid,
+                        const float *new_origin /* host[3] */, int64_t n_points,
+                        const float *proj, int n_views, int height, int width,
+                        int32_t *x, int32_t *y, uint8_t *valid, void *stream);
+
+/*
+ * ivx_backproject_scenes -- the fused hot path: for a batch of B scenes with V
+ * views each, project every voxel through every view, gather the C-channel
+ * feature of the rounded pixel, and reduce over views in registers.
+ * Replaces, per scene, backproject (detectors/imvoxelnet.py:145-160) and the
+ * view reduction of extract_feat (:70-74); the batch replaces the Python loop
+ * and torch.stack of :57-78.  The reference's [V,C,N] temporary never exists.
+ *
+ *   feat          fp32 feature maps, logical shape [B][V][C][Hf][Wf], addressed
+ *                 through feat_strides (host, 5 element strides: b, v, c, h, w).
+ *                 Channels-last maps (stride_c == 1, C % 4 == 0, 16-byte aligned
+ *                 rows) take the vectorised kernel; anything else (e.g. the
+ *                 reference's NCHW slice of :69) takes the strided kernel.
+ *   hw            host [B][2] int32: un-padded (height, width) of each scene's
+ *                 map, img_shape // stride (:67-68).  Pixels outside are invalid.
+ *   proj          [B][V][12] fp32
+ *   points        [3][N] fp32 shared by all scenes, or NULL to use `grid` with
+ *                 new_origin (host [B][3]; scenes may have different origins)
+ *   volume        out, element (b, c, n) at  b*vol_strides[0] + c*vol_strides[1]
+ *                 + n*vol_strides[2]  (host, 3 element strides): {C*N, N, 1} is
+ *                 the reference's [B,C,X,Y,Z]; {N*C, 1, C} is channels-last
+ *                 (NDHWC) which the 3D-neck kernels consume and which stores
+ *                 fully coalesced.  vol_dtype IVX_BF16 is allowed with MEAN only.
+ *   valid         [B][N] uint8 out (count > 0), may be NULL
+ *   count         [B][N] int32 out (number of valid views), may be NULL;
+ *                 required for IVX_REDUCE_PARTIAL
+ */
+IVX_API int ivx_backproject_scenes(const float *feat, const int64_t *feat_strides /* host[5] */,
+                           int n_scenes, int n_views, int n_channels,
+                           const int32_t *hw /* host[B][2] */, const float *proj,
+                           const float *points, const ivx_grid *grid,
+                           const float *new_origin /* host[B][3] */, int64_t n_points,
+                           void *volume, const int64_t *vol_strides /* host[3] */,
+                           int vol_dtype, int reduce, uint8_t *valid, int32_t *count,
+                           void *stream);
+
+/*
+ * ivx_backproject_views -- strict drop-in for the reference function
+ * backproject(features, points, projection) (detectors/imvoxelnet.py:145-160):
+ * per-view volumes [V][C][N] fp32 (zeros where invalid) and valid [V][N].
+ * volume element (v, c, n) is at v*vol_strides[0] + c*vol_strides[1] +
+ * n*vol_strides[2].  feat_strides: host, 4 element strides (v, c, h, w).
+ */
+IVX_API int ivx_backproject_views(const float *feat, const int64_t *feat_strides /* host[4] */,
+                          int n_views, int n_channels, int height, int width,
+                          const float *proj, const float *points, const ivx_grid *grid,
+                          const float *new_origin /* host[3] */, int64_t n_points,
+                          float *volume, const int64_t *vol_strides /* host[3] */,
+                          uint8_t *valid, void *stream);
+
+/*
+ * ivx_finalize_mean -- second half of the view-sharded (multi-GPU) path: after
+ * the ranks' IVX_REDUCE_PARTIAL sums and counts have been all-reduced, divide
+ * and zero the unseen voxels (detectors/imvoxelnet.py:72-74).
+ *   sum     [B][N][C] fp32 (channels-last partial sums), count [B][N] int32
+ *   volume  out, addressed like ivx_backproject_scenes' volume; valid [B][N]
+ */
+IVX_API int ivx_finalize_mean(const float *sum, const int32_t *count, int n_scenes,
+                      int n_channels, int64_t n_points, void *volume,
+                      const int64_t *vol_strides /* host[3] */, int vol_dtype,
+                      uint8_t *valid, void *stream);
+
+/*
+ * ivx_repack_nchw_to_nhwc -- layout pass for callers that hold the reference's
+ * NCHW maps: dst[i][y][x][c] = src[i][c][y][x] for i < n_images (tiled through
+ * shared memory, coalesced on both sides).  src_strides: host, 4 element
+ * strides (image, c, h, w); dst is dense [n_images][H][W][C].
+ * Replaces nothing in the reference (it gathers 4-byte elements from NCHW at
+ * detectors/imvoxelnet.py:157); it exists so the gather can be 128-bit wide.
+ */
+IVX_API int ivx_repack_nchw_to_nhwc(const float *src, const int64_t *src_strides /* host[4] */,
+                            int n_images, int n_channels, int height, int width,
+                            float *dst, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IVX_H_ */

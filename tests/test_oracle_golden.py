@@ -169,3 +169,20 @@ def test_against_live_reference(seed):
     vol, valid = ob.backproject(feats.numpy(), pts.numpy(), P.numpy())
     assert np.array_equal(valid, valid_ref.numpy())
     assert np.array_equal(vol, vol_ref.numpy())
+
+
+@pytest.mark.parametrize("name", SMALL)
+def test_torch_port_matches_golden(golden_dir, name):
+    """The torch-CPU port timed as the CPU baseline computes the reference's
+    numbers exactly (same ATen ops)."""
+    from oracle import torch_port
+    g = _load(golden_dir, name)
+    h, w = int(g["h"]), int(g["w"])
+    feats = torch.from_numpy(g["features"])[:, :, :h, :w]
+    pts, P = torch.from_numpy(g["points"]), torch.from_numpy(g["projection"])
+    vol, valid = torch_port.backproject(feats, pts, P)
+    assert np.array_equal(vol.numpy(), g["volume_views"])
+    assert np.array_equal(valid.numpy(), g["valid_views"])
+    mean, seen = torch_port.scene_volume(feats, pts, P)
+    assert np.array_equal(seen.numpy(), g["valid"])
+    assert np.array_equal(mean.numpy(), g["volume"])
