@@ -8,14 +8,18 @@
 //
 // Work decomposition (both kernels):
 //   * a warp owns a tile of T consecutive voxels of one scene;
-//   * phase 1 -- all 32 lanes project (voxel, view) pairs of the tile and
-//     leave, per voxel, one int32 per view in a shared-memory table: the
-//     offset of the hit pixel, or -1.  The 3x4 matrices sit in shared memory,
-//     voxel coordinates are rebuilt in registers from the grid description;
-//   * phase 2 -- G lanes own one voxel: they compact the table row with a
-//     ballot, then stream the C contiguous channels of each hit pixel with
-//     128-bit loads (several pixels in flight), accumulating sum and count in
-//     registers; the epilogue divides, zeroes unseen voxels and stores.
+//   * phase 1 -- all 32 lanes project (voxel, view) pairs of the tile.  The
+//     3x4 matrices sit in shared memory, voxel coordinates are rebuilt in
+//     registers from the grid description.  Hits are compacted on the fly
+//     (ballot + popc) into a per-voxel list of pixel offsets in shared memory,
+//     in ascending view order; single-view scenes keep the one offset in a
+//     register instead;
+//   * phase 2 -- G lanes own one voxel: they walk its hit list four pixels at
+//     a time and stream the C contiguous channels of each pixel with 128-bit
+//     loads (all four in flight), accumulating the sum in registers; the
+//     epilogue divides by the hit count, zeroes unseen voxels and stores with
+//     streaming 128-bit stores.  Single-view scenes instead keep four voxels
+//     per group in flight, since a voxel has at most one pixel to fetch.
 //
 // Bit-exactness of the pixel index (checked against the reference's outputs):
 // the K=4 dot product is evaluated as rn(P0*x) then three fma's -- what the
@@ -28,14 +32,37 @@
 
 namespace ivx {
 
+// floor(n / d) for 0 <= n < 2^31 as one multiply-high and a shift
+// (Granlund-Montgomery with p = 31 + ceil(log2 d)); d == 1 is flagged by m == 0.
+struct FastDiv {
+    unsigned m;
+    int s;
+    __device__ __forceinline__ int div(int n) const {
+        return m ? (int)(__umulhi((unsigned)n, m) >> s) : n;
+    }
+};
+
+static FastDiv make_fastdiv(int d) {
+    FastDiv f = {0u, 0};
+    if (d <= 1) return f;
+    int lg = 0;
+    while ((1ll << lg) < d) ++lg;
+    const int p = 31 + lg;
+    f.m = (unsigned)(((1ull << p) + (unsigned long long)d - 1) / (unsigned long long)d);
+    f.s = p - 32;
+    return f;
+}
+
 struct BpArgs {
     const float *feat;
     long long fs_b, fs_v, fs_c, fs_h, fs_w;  // element strides of [B][V][C][H][W]
+    int q_v, q_h, q_w;                       // the same in float4 units (vectorised kernel)
     const float *proj;                       // [B][V][12]
     long long proj_stride_b;                 // elements between scenes' matrix blocks
     const float *points;                     // [3][N] or nullptr
     float vs[3];
     int V, C, X, Y, Z, N;
+    FastDiv div_z, div_y;
     void *vol;
     long long os_b, os_c, os_n;
     uint8_t *valid;  // [B][N]
@@ -75,39 +102,62 @@ __device__ __forceinline__ void voxel_coords(const BpArgs &a, int b, int n, floa
         py = __ldg(a.points + a.N + n);
         pz = __ldg(a.points + 2ll * a.N + n);
     } else {
-        const int iz = n % a.Z;
-        const int t = n / a.Z;
-        const int iy = t % a.Y;
-        const int ix = t / a.Y;
+        const int t = a.div_z.div(n);
+        const int iz = n - t * a.Z;
+        const int ix = a.div_y.div(t);
+        const int iy = t - ix * a.Y;
         px = __fadd_rn(__fmul_rn((float)ix, a.vs[0]), a.new_origin[b][0]);
         py = __fadd_rn(__fmul_rn((float)iy, a.vs[1]), a.new_origin[b][1]);
         pz = __fadd_rn(__fmul_rn((float)iz, a.vs[2]), a.new_origin[b][2]);
     }
 }
 
-// Phase 1.  table[j * stride + v] = offset of the pixel voxel j hits in view v
-// (in units of `1 << OFF_SHIFT` elements), or -1.
-template <int OFF_SHIFT>
-__device__ __forceinline__ void fill_table(const BpArgs &a, const float *sP, int *table, int b,
-                                           int n0, int lane) {
+// Phase 1.  For every voxel j of the tile, row j of `table` receives the
+// offsets of the pixels it hits, in ascending view order (float4 units if VEC,
+// else elements); the return value is the number of hits of the voxel this
+// lane works for (lane & (T-1)), identical on all lanes of that voxel.  The
+// per-voxel valid flag and view count are stored from here, 32 voxels per
+// coalesced store.
+template <bool VEC>
+__device__ __forceinline__ int fill_table(const BpArgs &a, const float *sP, int *table, int b,
+                                          int n0, int lane) {
+    constexpr unsigned FULL = 0xffffffffu;
     const int T = 1 << a.tile_log2;
     const int j = lane & (T - 1);
     const int vq = lane >> a.tile_log2;
     const int vstep = 32 >> a.tile_log2;
     const int n = n0 + j;
-    if (n < a.N) {
-        float px, py, pz;
-        voxel_coords(a, b, n, px, py, pz);
-        const int h = a.hw[b][0], w = a.hw[b][1];
-        for (int v = vq; v < a.V; v += vstep) {
+    // lanes j, j+T, j+2T, ... work for voxel j on consecutive views
+    unsigned pattern = 0;
+    for (int q = 0; q < vstep; ++q) pattern |= 1u << (j + (q << a.tile_log2));
+    const unsigned below = pattern & ((1u << lane) - 1u);
+    float px = 0.f, py = 0.f, pz = 0.f;
+    if (n < a.N) voxel_coords(a, b, n, px, py, pz);
+    const int h = a.hw[b][0], w = a.hw[b][1];
+    int *row = table + j * a.table_stride;
+    int base = 0;
+    for (int v0 = 0; v0 < a.V; v0 += vstep) {
+        const int v = v0 + vq;
+        bool ok = false;
+        int off = 0;
+        if (n < a.N && v < a.V) {
             float xr, yr;
-            const bool ok = project_rn(sP + 12 * v, px, py, pz, h, w, xr, yr);
-            long long off = -1;
-            if (ok) off = (v * a.fs_v + (long long)yr * a.fs_h + (long long)xr * a.fs_w) >> OFF_SHIFT;
-            table[j * a.table_stride + v] = (int)off;
+            ok = project_rn(sP + 12 * v, px, py, pz, h, w, xr, yr);
+            if (VEC)
+                off = v * a.q_v + (int)yr * a.q_h + (int)xr * a.q_w;
+            else
+                off = (int)(v * a.fs_v + (long long)yr * a.fs_h + (long long)xr * a.fs_w);
         }
+        const unsigned m = __ballot_sync(FULL, ok);
+        if (ok) row[base + __popc(m & below)] = off;
+        base += __popc(m & pattern);
+    }
+    if (lane < T && n < a.N) {
+        if (a.valid) a.valid[(long long)b * a.N + n] = base > 0;
+        if (a.count) a.count[(long long)b * a.N + n] = base;
     }
     __syncwarp();
+    return base;
 }
 
 template <typename OutT>
@@ -131,12 +181,70 @@ __device__ __forceinline__ void store4<__nv_bfloat16>(__nv_bfloat16 *p, float4 v
 // ---------------------------------------------------------------------------
 // Vectorised kernel: channels-last features (fs_c == 1), channels-last volume
 // (os_c == 1).  G lanes per voxel, CPL float4 per lane; G * CPL * 4 >= C.
+// Three schedules of phase 2, chosen by the number of views:
+//   MODE_DEEP   one voxel per group at a time, DEPTH pixels of it in flight
+//               (many views: the hit list of a voxel is long);
+//   MODE_WIDE   WIDTH voxels per group at a time, one pixel of each in flight
+//               (few views: most hit lists hold 0..2 pixels);
+//   MODE_SINGLE one view: no table at all, the offset stays in a register and
+//               the mean is the feature itself.
 // ---------------------------------------------------------------------------
-template <int G, int CPL, typename OutT>
+enum { MODE_DEEP = 0, MODE_SINGLE = 1, MODE_WIDE = 2 };
+
+template <int CPL>
+__device__ __forceinline__ void zero4(float4 (&acc)[CPL]) {
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+}
+
+template <int G, int CPL>
+__device__ __forceinline__ void gather4(const float4 *feat4, int off, int t, const bool (&ch_ok)[CPL],
+                                        float4 (&r)[CPL]) {
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        r[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (off >= 0 && ch_ok[i]) r[i] = __ldg(feat4 + off + t + i * G);
+    }
+}
+
+template <int CPL>
+__device__ __forceinline__ void add4(float4 (&acc)[CPL], const float4 (&r)[CPL]) {
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        acc[i].x += r[i].x;
+        acc[i].y += r[i].y;
+        acc[i].z += r[i].z;
+        acc[i].w += r[i].w;
+    }
+}
+
+// sum / count (count converted to float, :72; 0 where unseen, :74), then store
+template <int G, int CPL, bool DIVIDE, typename OutT>
+__device__ __forceinline__ void finish_voxel(const BpArgs &a, OutT *vol, int n, int t, int cnt,
+                                             float4 (&acc)[CPL], const bool (&ch_ok)[CPL]) {
+    if (DIVIDE && a.reduce == IVX_REDUCE_MEAN && cnt > 1) {
+        const float c = (float)cnt;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            acc[i].x = __fdiv_rn(acc[i].x, c);
+            acc[i].y = __fdiv_rn(acc[i].y, c);
+            acc[i].z = __fdiv_rn(acc[i].z, c);
+            acc[i].w = __fdiv_rn(acc[i].w, c);
+        }
+    }  // cnt == 1: x / 1.0f == x;  cnt == 0: the accumulator is still zero
+    OutT *dst = vol + (long long)n * a.os_n;
+#pragma unroll
+    for (int i = 0; i < CPL; ++i)
+        if (ch_ok[i]) store4<OutT>(dst + (t + i * G) * 4, acc[i]);
+}
+
+template <int G, int CPL, int MODE, typename OutT>
 __global__ void __launch_bounds__(256) bp_vec_kernel(const __grid_constant__ BpArgs a) {
     extern __shared__ int smem[];
     constexpr unsigned FULL = 0xffffffffu;
-    constexpr int UNROLL = (CPL >= 4) ? 2 : 4;  // pixels in flight per voxel
+    constexpr int VPI = 32 / G;                // voxels a warp works on at once
+    constexpr int DEPTH = (CPL >= 4) ? 2 : 4;  // MODE_DEEP: pixels in flight per voxel
+    constexpr int WIDTH = (CPL >= 4) ? 1 : (CPL == 2 ? 2 : 4);  // voxels in flight per group
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -161,76 +269,99 @@ __global__ void __launch_bounds__(256) bp_vec_kernel(const __grid_constant__ BpA
 
     for (int tile = blockIdx.x * nwarps + warp; tile < ntiles; tile += gridDim.x * nwarps) {
         const int n0 = tile << a.tile_log2;
-        fill_table<2>(a, sP, table, b, n0, lane);
 
-        for (int j0 = 0; j0 < T; j0 += 32 / G) {
-            const int j = j0 + g;
-            const int n = n0 + j;
-            const bool active = (j < T) && (n < a.N);
-            float4 acc[CPL];
-#pragma unroll
-            for (int i = 0; i < CPL; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-            int cnt = 0;
-
-            for (int c0 = 0; c0 < a.V; c0 += G) {
-                const int v = c0 + t;
-                const int off = (active && v < a.V) ? table[j * a.table_stride + v] : -1;
-                const unsigned m = __ballot_sync(FULL, off >= 0);
-                unsigned gm = (G == 32) ? m : ((m >> (g * G)) & ((1u << (G & 31)) - 1u));
-                cnt += __popc(gm);
-                while (__any_sync(FULL, gm != 0)) {
-                    int o[UNROLL];
-#pragma unroll
-                    for (int u = 0; u < UNROLL; ++u) {
-                        const bool has = gm != 0;
-                        const int src = has ? (__ffs(gm) - 1) : 0;
-                        gm &= gm - 1;  // 0 stays 0
-                        const int ov = __shfl_sync(FULL, off, src, G);
-                        o[u] = has ? ov : -1;
-                    }
-                    float4 r[UNROLL][CPL];
-#pragma unroll
-                    for (int u = 0; u < UNROLL; ++u)
-#pragma unroll
-                        for (int i = 0; i < CPL; ++i) {
-                            r[u][i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                            if (o[u] >= 0 && ch_ok[i]) r[u][i] = __ldg(feat4 + o[u] + t + i * G);
-                        }
-#pragma unroll
-                    for (int u = 0; u < UNROLL; ++u)  // ascending view order
-#pragma unroll
-                        for (int i = 0; i < CPL; ++i) {
-                            acc[i].x += r[u][i].x;
-                            acc[i].y += r[u][i].y;
-                            acc[i].z += r[u][i].z;
-                            acc[i].w += r[u][i].w;
-                        }
+        if constexpr (MODE == MODE_SINGLE) {
+            // lane j projects voxel j and keeps the offset of its pixel
+            int my_off = -1;
+            {
+                const int n = n0 + lane;
+                if (lane < T && n < a.N) {
+                    float px, py, pz, xr, yr;
+                    voxel_coords(a, b, n, px, py, pz);
+                    if (project_rn(sP, px, py, pz, a.hw[b][0], a.hw[b][1], xr, yr))
+                        my_off = (int)yr * a.q_h + (int)xr * a.q_w;
+                    if (a.valid) a.valid[(long long)b * a.N + n] = my_off >= 0;
+                    if (a.count) a.count[(long long)b * a.N + n] = my_off >= 0;
                 }
             }
-
-            if (active) {
-                if (a.reduce == IVX_REDUCE_MEAN) {
-                    // sum / count (count converted to float, :72); 0 where unseen (:74)
-                    const float c = (float)cnt;
+            for (int j0 = 0; j0 < T; j0 += VPI * WIDTH) {
+                int o[WIDTH];
+                float4 r[WIDTH][CPL];
 #pragma unroll
-                    for (int i = 0; i < CPL; ++i) {
-                        acc[i].x = cnt ? __fdiv_rn(acc[i].x, c) : 0.f;
-                        acc[i].y = cnt ? __fdiv_rn(acc[i].y, c) : 0.f;
-                        acc[i].z = cnt ? __fdiv_rn(acc[i].z, c) : 0.f;
-                        acc[i].w = cnt ? __fdiv_rn(acc[i].w, c) : 0.f;
-                    }
+                for (int u = 0; u < WIDTH; ++u) {
+                    const int j = j0 + u * VPI + g;
+                    o[u] = __shfl_sync(FULL, my_off, j & 31);
+                    if (j >= T) o[u] = -1;
                 }
-                OutT *dst = vol + (long long)n * a.os_n;
 #pragma unroll
-                for (int i = 0; i < CPL; ++i)
-                    if (ch_ok[i]) store4<OutT>(dst + (t + i * G) * 4, acc[i]);
-                if (t == 0) {
-                    if (a.valid) a.valid[(long long)b * a.N + n] = cnt > 0;
-                    if (a.count) a.count[(long long)b * a.N + n] = cnt;
+                for (int u = 0; u < WIDTH; ++u) gather4<G, CPL>(feat4, o[u], t, ch_ok, r[u]);
+#pragma unroll
+                for (int u = 0; u < WIDTH; ++u) {
+                    const int j = j0 + u * VPI + g;
+                    const int n = n0 + j;
+                    if (j < T && n < a.N)
+                        finish_voxel<G, CPL, false, OutT>(a, vol, n, t, o[u] >= 0, r[u], ch_ok);
                 }
             }
+        } else if constexpr (MODE == MODE_WIDE) {
+            const int my_cnt = fill_table<true>(a, sP, table, b, n0, lane);
+            for (int j0 = 0; j0 < T; j0 += VPI * WIDTH) {
+                int cnt[WIDTH];
+                float4 acc[WIDTH][CPL];
+                int most = 0;
+#pragma unroll
+                for (int u = 0; u < WIDTH; ++u) {
+                    const int j = j0 + u * VPI + g;
+                    cnt[u] = __shfl_sync(FULL, my_cnt, j & 31);
+                    if (j >= T || n0 + j >= a.N) cnt[u] = 0;
+                    most = max(most, cnt[u]);
+                    zero4<CPL>(acc[u]);
+                }
+                const int *rows = table + (j0 + g) * a.table_stride;
+                for (int k = 0; k < most; ++k) {
+                    float4 r[WIDTH][CPL];
+#pragma unroll
+                    for (int u = 0; u < WIDTH; ++u) {
+                        const int o = (k < cnt[u]) ? rows[u * VPI * a.table_stride + k] : -1;
+                        gather4<G, CPL>(feat4, o, t, ch_ok, r[u]);
+                    }
+#pragma unroll
+                    for (int u = 0; u < WIDTH; ++u) add4<CPL>(acc[u], r[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < WIDTH; ++u) {
+                    const int j = j0 + u * VPI + g;
+                    const int n = n0 + j;
+                    if (j < T && n < a.N)
+                        finish_voxel<G, CPL, true, OutT>(a, vol, n, t, cnt[u], acc[u], ch_ok);
+                }
+            }
+            __syncwarp();  // the table is rewritten by the next tile
+        } else {
+            const int my_cnt = fill_table<true>(a, sP, table, b, n0, lane);
+            for (int j0 = 0; j0 < T; j0 += VPI) {
+                const int j = j0 + g;
+                const int n = n0 + j;
+                const bool active = (j < T) && (n < a.N);
+                int cnt = __shfl_sync(FULL, my_cnt, j & 31);
+                if (!active) cnt = 0;
+                const int *row = table + j * a.table_stride;
+                float4 acc[CPL];
+                zero4<CPL>(acc);
+                for (int k0 = 0; k0 < cnt; k0 += DEPTH) {
+                    float4 r[DEPTH][CPL];
+#pragma unroll
+                    for (int u = 0; u < DEPTH; ++u) {
+                        const int o = (k0 + u < cnt) ? row[k0 + u] : -1;
+                        gather4<G, CPL>(feat4, o, t, ch_ok, r[u]);
+                    }
+#pragma unroll
+                    for (int u = 0; u < DEPTH; ++u) add4<CPL>(acc, r[u]);  // ascending view order
+                }
+                if (active) finish_voxel<G, CPL, true, OutT>(a, vol, n, t, cnt, acc, ch_ok);
+            }
+            __syncwarp();  // the table is rewritten by the next tile
         }
-        __syncwarp();  // table is rewritten by the next tile
     }
 }
 
@@ -259,33 +390,21 @@ __global__ void __launch_bounds__(256) bp_strided_kernel(const __grid_constant__
 
     for (int tile = blockIdx.x * nwarps + warp; tile < ntiles; tile += gridDim.x * nwarps) {
         const int n0 = tile << a.tile_log2;
-        fill_table<0>(a, sP, table, b, n0, lane);
+        const int my_cnt = fill_table<false>(a, sP, table, b, n0, lane);
         for (int j = 0; j < T; ++j) {
             const int n = n0 + j;
             if (n >= a.N) break;
             const int *row = table + j * a.table_stride;
-            int cnt = 0;
-            for (int c0 = 0; c0 < a.V; c0 += 32) {
-                const int v = c0 + lane;
-                const int off = v < a.V ? row[v] : -1;
-                cnt += __popc(__ballot_sync(FULL, off >= 0));
-            }
+            const int cnt = __shfl_sync(FULL, my_cnt, j);
             const float fc = (float)cnt;
             for (int cb = 0; cb < a.C; cb += 32) {
                 const int c = cb + lane;
                 if (c < a.C) {
                     float acc = 0.f;
-                    for (int v = 0; v < a.V; ++v) {
-                        const int off = row[v];
-                        if (off >= 0) acc += __ldg(feat + off + c * a.fs_c);
-                    }
+                    for (int k = 0; k < cnt; ++k) acc += __ldg(feat + row[k] + c * a.fs_c);
                     if (a.reduce == IVX_REDUCE_MEAN) acc = cnt ? __fdiv_rn(acc, fc) : 0.f;
                     vol[c * a.os_c + (long long)n * a.os_n] = acc;
                 }
-            }
-            if (lane == 0) {
-                if (a.valid) a.valid[(long long)b * a.N + n] = cnt > 0;
-                if (a.count) a.count[(long long)b * a.N + n] = cnt;
             }
         }
         __syncwarp();
@@ -387,25 +506,37 @@ __global__ void __launch_bounds__(256) repack_nchw_nhwc_kernel(
 
 // ------------------------------- host side --------------------------------
 
-static int pick_tile_log2(long long n_points, int n_scenes) {
-    // largest tile that still gives every SM ~32 warps of work
-    for (int lg = 5; lg > 2; --lg) {
+static int pick_tile_log2(long long n_points, int n_scenes, int table_stride) {
+    // largest tile whose hit table stays small (<= 2 KB per warp keeps the
+    // occupancy register-bound) and that still gives every SM ~32 warps of work
+    int lg = 5;
+    while (lg > 2 && (1 << lg) * table_stride > 512) --lg;
+    for (; lg > 2; --lg) {
         const long long tiles = ((n_points + (1 << lg) - 1) >> lg) * n_scenes;
-        if (tiles >= (long long)kNumSMs * 32) return lg;
+        if (tiles >= (long long)kNumSMs * 32) break;
     }
-    return 2;
+    return lg;
 }
 
-template <typename OutT>
+template <int MODE, typename OutT>
 static void *pick_vec_kernel(int C) {
     const int c4 = (C + 3) / 4;
-    if (c4 <= 8) return (void *)bp_vec_kernel<8, 1, OutT>;
-    if (c4 <= 16) return (void *)bp_vec_kernel<16, 1, OutT>;
-    if (c4 <= 32) return (void *)bp_vec_kernel<32, 1, OutT>;
-    if (c4 <= 64) return (void *)bp_vec_kernel<32, 2, OutT>;
-    if (c4 <= 128) return (void *)bp_vec_kernel<32, 4, OutT>;
-    if (c4 <= 256) return (void *)bp_vec_kernel<32, 8, OutT>;
+    if (c4 <= 8) return (void *)bp_vec_kernel<8, 1, MODE, OutT>;
+    if (c4 <= 16) return (void *)bp_vec_kernel<16, 1, MODE, OutT>;
+    if (c4 <= 32) return (void *)bp_vec_kernel<32, 1, MODE, OutT>;
+    if (c4 <= 64) return (void *)bp_vec_kernel<32, 2, MODE, OutT>;
+    if (c4 <= 128) return (void *)bp_vec_kernel<32, 4, MODE, OutT>;
+    if (c4 <= 256) return (void *)bp_vec_kernel<32, 8, MODE, OutT>;
     return nullptr;
+}
+
+constexpr int kWideMaxViews = 8;  // up to here most voxels are hit by 0..2 views
+
+template <typename OutT>
+static void *pick_vec_kernel(int C, int V) {
+    if (V == 1) return pick_vec_kernel<MODE_SINGLE, OutT>(C);
+    if (V <= kWideMaxViews) return pick_vec_kernel<MODE_WIDE, OutT>(C);
+    return pick_vec_kernel<MODE_DEEP, OutT>(C);
 }
 
 static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
@@ -419,7 +550,19 @@ static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t st
                          (reinterpret_cast<uintptr_t>(a.vol) % (4 * esz)) == 0;
     void *kernel = nullptr;
     if (feat_vec && vol_vec)
-        kernel = vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16>(a.C) : pick_vec_kernel<float>(a.C);
+        kernel = vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16>(a.C, a.V)
+                                        : pick_vec_kernel<float>(a.C, a.V);
+    if (kernel != nullptr) {
+        // table entries are int32 offsets in float4 units inside one scene's block
+        long long hmax = 0, wmax = 0;
+        for (int b = 0; b < n_scenes; ++b) {
+            hmax = a.hw[b][0] > hmax ? a.hw[b][0] : hmax;
+            wmax = a.hw[b][1] > wmax ? a.hw[b][1] : wmax;
+        }
+        if ((llabs(a.fs_v) * a.V + llabs(a.fs_h) * hmax + llabs(a.fs_w) * wmax) / 4 >= (1ll << 31))
+            return fail(IVX_ERR_UNSUPPORTED, "feature block of one scene exceeds 2^33 elements");
+        a.q_v = (int)(a.fs_v / 4), a.q_h = (int)(a.fs_h / 4), a.q_w = (int)(a.fs_w / 4);
+    }
     if (kernel == nullptr) {
         if (vol_dtype != IVX_F32)
             return fail(IVX_ERR_UNSUPPORTED,
@@ -436,8 +579,8 @@ static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t st
             return fail(IVX_ERR_UNSUPPORTED, "feature block of one scene exceeds 2^31 elements");
     }
 
-    a.tile_log2 = pick_tile_log2(a.N, n_scenes);
-    a.table_stride = a.V | 1;
+    a.table_stride = (a.V + 3) & ~3;
+    a.tile_log2 = pick_tile_log2(a.N, n_scenes, a.table_stride);
     const int T = 1 << a.tile_log2;
     const size_t proj_words = (a.V * 12 + 3) & ~3;
     int warps = 8;
@@ -494,9 +637,12 @@ static int backproject_batch(const float *feat, const long long fs[5], int B, in
         a.points = points;
         a.V = V, a.C = C, a.N = (int)N;
         a.X = a.Y = a.Z = 1;
+        a.div_z = a.div_y = make_fastdiv(1);
+        a.q_v = a.q_h = a.q_w = 0;
         a.vs[0] = a.vs[1] = a.vs[2] = 0.f;
         if (points == nullptr) {
             a.X = grid->n_voxels[0], a.Y = grid->n_voxels[1], a.Z = grid->n_voxels[2];
+            a.div_z = make_fastdiv(a.Z), a.div_y = make_fastdiv(a.Y);
             for (int k = 0; k < 3; ++k) a.vs[k] = grid->voxel_size[k];
         }
         a.vol = static_cast<char *>(volume) + (size_t)(b0 * vs[0]) * esz;

@@ -5,6 +5,8 @@ Same names, argument meaning and returns as the reference's functions in
 reduction of ``extract_feat`` :70-74), implemented by the C-ABI library
 through ``_lib``.  PyTorch is used for device memory and streams only.
 """
+import functools
+
 import numpy as np
 import torch
 
@@ -20,6 +22,18 @@ _launches = 0
 
 def launch_count():
     return _launches
+
+
+@functools.lru_cache(maxsize=4096)
+def _new_origin_cached(n_voxels, voxel_size, origin):
+    return tuple(grid_new_origin(n_voxels, voxel_size, origin).tolist())
+
+
+def _new_origin(n_voxels, voxel_size, origin):
+    """fp32 ``origin - n_voxels / 2 * voxel_size`` (projection.grid_new_origin),
+    memoised: the same few origins come back every batch."""
+    return _new_origin_cached(tuple(int(v) for v in n_voxels), tuple(float(v) for v in voxel_size),
+                              tuple(float(v) for v in origin))
 
 
 def _stream():
@@ -67,7 +81,7 @@ def project_indices(points, projection, height, width, *, n_voxels=None, voxel_s
     else:
         device = torch.device(device or "cuda")
         g = _lib.grid(n_voxels, voxel_size)
-        no = _lib.f32(grid_new_origin(n_voxels, voxel_size, origin).tolist())
+        no = _lib.f32(_new_origin(n_voxels, voxel_size, origin))
         n, pp = int(np.prod(n_voxels)), None
     proj = _proj_dev(projection, device).reshape(-1, 12)
     v = proj.shape[0]
@@ -153,7 +167,7 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
         pp, g = None, _lib.grid(n_voxels, voxel_size)
         flat = []
         for o in origins:
-            flat += grid_new_origin(n_voxels, voxel_size, o).tolist()
+            flat += _new_origin(n_voxels, voxel_size, o)
         if len(flat) != 3 * b:
             raise ValueError("origins must hold one origin per scene")
         no = _lib.f32(flat)
