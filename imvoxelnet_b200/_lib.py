@@ -38,7 +38,12 @@ PROTOTYPES = {
     "ivx_finalize_mean": [c_void_p, c_void_p, c_int, c_int, c_int64, c_void_p, _i64p, c_int,
                           c_void_p, c_void_p],
     "ivx_repack_nchw_to_nhwc": [c_void_p, _i64p, c_int, c_int, c_int, c_int, c_void_p, c_void_p],
+    "ivx_backproject_nchw_workspace_bytes": [c_int, c_int, c_int, _i32p],
+    "ivx_backproject_scenes_nchw": [c_void_p, _i64p, c_int, c_int, c_int, _i32p, c_void_p, c_void_p,
+                                    _GridP, _f32p, c_int64, c_void_p, _i64p, c_int, c_int, c_void_p,
+                                    c_void_p, c_void_p, c_int64, c_void_p],
 }
+RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64}
 
 _lib = None
 
@@ -62,7 +67,7 @@ def lib():
         for name, argtypes in PROTOTYPES.items():
             fn = getattr(handle, name)
             fn.argtypes = argtypes
-            fn.restype = c_int
+            fn.restype = RESTYPES.get(name, c_int)
         _lib = handle
     return _lib
 

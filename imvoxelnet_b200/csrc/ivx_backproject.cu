@@ -479,11 +479,15 @@ __global__ void __launch_bounds__(256) finalize_mean_kernel(
 }
 
 // NCHW -> NHWC through a 32x33 shared-memory tile, coalesced on both sides.
+// Images are indexed (outer, inner) with their own strides so that a [B][V]
+// batch of maps needs one launch; dst is dense [outer*inner][H][W][C].
 __global__ void __launch_bounds__(256) repack_nchw_nhwc_kernel(
-    const float *__restrict__ src, long long s_i, long long s_c, long long s_h, long long s_w,
-    int C, int H, int W, float *__restrict__ dst) {
+    const float *__restrict__ src, int n_inner, long long s_o, long long s_i, long long s_c,
+    long long s_h, long long s_w, int C, int H, int W, float *__restrict__ dst) {
     __shared__ float tile[32][33];
     const int img = blockIdx.z;
+    const int io = img / n_inner, ii = img - io * n_inner;
+    const float *base = src + io * s_o + ii * s_i;
     const int HW = H * W;
     const int p0 = blockIdx.x * 32;  // pixel tile
     const int c0 = blockIdx.y * 32;  // channel tile
@@ -493,7 +497,7 @@ __global__ void __launch_bounds__(256) repack_nchw_nhwc_kernel(
         float v = 0.f;
         if (c < C && p < HW) {
             const int yy = p / W, xx = p - yy * W;
-            v = __ldcs(src + img * s_i + c * s_c + yy * s_h + xx * s_w);
+            v = __ldcs(base + c * s_c + yy * s_h + xx * s_w);
         }
         tile[r][tx] = v;
     }
@@ -502,6 +506,18 @@ __global__ void __launch_bounds__(256) repack_nchw_nhwc_kernel(
         const int p = p0 + r, c = c0 + tx;
         if (c < C && p < HW) dst[((long long)img * HW + p) * C + c] = tile[tx][r];
     }
+}
+
+static int launch_repack(const float *src, int n_outer, int n_inner, long long s_o, long long s_i,
+                         long long s_c, long long s_h, long long s_w, int C, int H, int W, float *dst,
+                         cudaStream_t stream) {
+    const long long hw = (long long)H * W;
+    IVX_REQUIRE(hw < (1ll << 31) && (C + 31) / 32 <= 65535 && (long long)n_outer * n_inner <= 65535,
+                "map or batch too large for the repack kernel");
+    dim3 grid((unsigned)((hw + 31) / 32), (unsigned)((C + 31) / 32), (unsigned)(n_outer * n_inner));
+    repack_nchw_nhwc_kernel<<<grid, 256, 0, stream>>>(src, n_inner, s_o, s_i, s_c, s_h, s_w, C, H, W, dst);
+    IVX_CHECK_LAUNCH("repack launch");
+    return IVX_OK;
 }
 
 // ------------------------------- host side --------------------------------
@@ -762,12 +778,53 @@ extern "C" int ivx_repack_nchw_to_nhwc(const float *src, const int64_t *src_stri
     IVX_REQUIRE(src && src_strides && dst, "NULL argument");
     IVX_REQUIRE(n_images > 0 && n_images <= 65535 && n_channels > 0 && height > 0 && width > 0,
                 "sizes out of range");
-    const long long hw = (long long)height * width;
-    IVX_REQUIRE(hw < (1ll << 31) && (n_channels + 31) / 32 <= 65535, "map too large");
-    dim3 grid((unsigned)((hw + 31) / 32), (unsigned)((n_channels + 31) / 32), (unsigned)n_images);
-    repack_nchw_nhwc_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
-        src, src_strides[0], src_strides[1], src_strides[2], src_strides[3], n_channels, height,
-        width, dst);
-    IVX_CHECK_LAUNCH("repack launch");
-    return IVX_OK;
+    return launch_repack(src, 1, n_images, 0, src_strides[0], src_strides[1], src_strides[2],
+                         src_strides[3], n_channels, height, width, dst, (cudaStream_t)stream);
+}
+
+static void max_hw(const int32_t *hw, int n_scenes, int &hmax, int &wmax) {
+    hmax = wmax = 0;
+    for (int b = 0; b < n_scenes; ++b) {
+        hmax = hw[2 * b] > hmax ? hw[2 * b] : hmax;
+        wmax = hw[2 * b + 1] > wmax ? hw[2 * b + 1] : wmax;
+    }
+}
+
+extern "C" int64_t ivx_backproject_nchw_workspace_bytes(int n_scenes, int n_views, int n_channels,
+                                                        const int32_t *hw) {
+    if (n_scenes <= 0 || n_views <= 0 || n_channels <= 0 || hw == nullptr) return 0;
+    int hmax, wmax;
+    max_hw(hw, n_scenes, hmax, wmax);
+    return (int64_t)n_scenes * n_views * hmax * wmax * n_channels * (int64_t)sizeof(float);
+}
+
+extern "C" int ivx_backproject_scenes_nchw(const float *feat, const int64_t *feat_strides,
+                                           int n_scenes, int n_views, int n_channels,
+                                           const int32_t *hw, const float *proj, const float *points,
+                                           const ivx_grid *grid, const float *new_origin,
+                                           int64_t n_points, void *volume, const int64_t *vol_strides,
+                                           int vol_dtype, int reduce, uint8_t *valid, int32_t *count,
+                                           void *workspace, int64_t workspace_bytes, void *stream) {
+    IVX_REQUIRE(feat && feat_strides && hw && workspace, "NULL argument");
+    IVX_REQUIRE(n_scenes > 0 && n_views > 0 && n_channels > 0, "sizes must be positive");
+    if (n_channels % 4 != 0)
+        return fail(IVX_ERR_UNSUPPORTED, "the repacking path needs C %% 4 == 0 (got %d)", n_channels);
+    for (int b = 0; b < n_scenes; ++b)
+        IVX_REQUIRE(hw[2 * b] > 0 && hw[2 * b + 1] > 0, "scene %d: height/width must be positive", b);
+    const int64_t need = ivx_backproject_nchw_workspace_bytes(n_scenes, n_views, n_channels, hw);
+    IVX_REQUIRE(workspace_bytes >= need, "workspace of %lld bytes is too small, %lld needed",
+                (long long)workspace_bytes, (long long)need);
+    IVX_REQUIRE(aligned16(workspace), "workspace must be 16-byte aligned");
+    int hmax, wmax;
+    max_hw(hw, n_scenes, hmax, wmax);
+    float *ws = static_cast<float *>(workspace);
+    int rc = launch_repack(feat, n_scenes, n_views, feat_strides[0], feat_strides[1], feat_strides[2],
+                           feat_strides[3], feat_strides[4], n_channels, hmax, wmax, ws,
+                           (cudaStream_t)stream);
+    if (rc != IVX_OK) return rc;
+    const int64_t row = (int64_t)wmax * n_channels, img = row * hmax;
+    const int64_t ws_strides[5] = {img * n_views, img, 1, row, n_channels};
+    return ivx_backproject_scenes(ws, ws_strides, n_scenes, n_views, n_channels, hw, proj, points,
+                                  grid, new_origin, n_points, volume, vol_strides, vol_dtype, reduce,
+                                  valid, count, stream);
 }

@@ -132,7 +132,7 @@ def backproject(features, points, projection):
 
 
 def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, *, points=None,
-                       out_dtype=torch.float32, channels_last=True, reduce="mean"):
+                       out_dtype=torch.float32, channels_last=True, reduce="mean", repack=True):
     """Fused back-projection + view reduction of a batch of scenes.
 
     Replaces the per-scene loop of ``extract_feat`` (:57-78): returns the
@@ -146,6 +146,9 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
                 if ``points`` ([3,X,Y,Z]) is given
     reduce      "mean" (the reference's result) or "partial" (fp32 sums and
                 counts for the view-sharded multi-GPU path)
+    repack      NCHW features with C % 4 == 0 are first re-laid to channels-last
+                in a scratch buffer (``ivx_backproject_scenes_nchw``); False
+                gathers from the strided maps directly
     """
     global _launches
     _need_cuda(features, "features")
@@ -179,11 +182,21 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
         volume = torch.empty((b, c, n), dtype=out_dtype, device=dev)
     valid = torch.empty((b, n), dtype=torch.bool, device=dev)
     count = torch.empty((b, n), dtype=torch.int32, device=dev)
+    args = (b, v, c, hw_arr, proj.data_ptr(), pp, g, no, n, volume.data_ptr(),
+            _lib.i64(volume.stride()), dt, mode, valid.data_ptr(), count.data_ptr())
     with torch.cuda.device(dev):
-        _lib.check(_lib.lib().ivx_backproject_scenes(
-            features.data_ptr(), _lib.i64(features.stride()), b, v, c, hw_arr, proj.data_ptr(), pp, g,
-            no, n, volume.data_ptr(), _lib.i64(volume.stride()), dt, mode, valid.data_ptr(),
-            count.data_ptr(), _stream()), "ivx_backproject_scenes")
+        if features.stride(2) != 1 and c % 4 == 0 and repack:
+            # the reference's NCHW maps: re-lay them in scratch, then the vectorised kernel
+            nbytes = _lib.lib().ivx_backproject_nchw_workspace_bytes(b, v, c, hw_arr)
+            workspace = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            _lib.check(_lib.lib().ivx_backproject_scenes_nchw(
+                features.data_ptr(), _lib.i64(features.stride()), *args, workspace.data_ptr(),
+                nbytes, _stream()), "ivx_backproject_scenes_nchw")
+            _launches += 1
+        else:
+            _lib.check(_lib.lib().ivx_backproject_scenes(
+                features.data_ptr(), _lib.i64(features.stride()), *args, _stream()),
+                "ivx_backproject_scenes")
     _launches += (b + 63) // 64
     return (volume.unflatten(2, (xs, ys, zs)), valid.view(b, 1, xs, ys, zs),
             count.view(b, xs, ys, zs))

@@ -168,6 +168,33 @@ IVX_API int ivx_repack_nchw_to_nhwc(const float *src, const int64_t *src_strides
                             int n_images, int n_channels, int height, int width,
                             float *dst, void *stream);
 
+/*
+ * ivx_backproject_scenes_nchw -- ivx_backproject_scenes for callers that hold
+ * the maps the way the reference does: NCHW, possibly a strided slice
+ * (detectors/imvoxelnet.py:50-51, :69).  The maps are first re-laid to
+ * channels-last in `workspace` (one tiled transpose over the region the
+ * scenes use, max over scenes of hw), then the vectorised kernel runs on the
+ * workspace; results are identical to ivx_backproject_scenes on the same
+ * values.  Needs C % 4 == 0 (IVX_ERR_UNSUPPORTED otherwise: pass the NCHW
+ * strides to ivx_backproject_scenes instead, which takes the strided kernel).
+ *
+ *   workspace        device scratch, 16-byte aligned, owned by the caller; its
+ *                    contents are undefined afterwards
+ *   workspace_bytes  must be >= ivx_backproject_nchw_workspace_bytes(...)
+ * All other arguments as in ivx_backproject_scenes.
+ */
+IVX_API int64_t ivx_backproject_nchw_workspace_bytes(int n_scenes, int n_views, int n_channels,
+                                                     const int32_t *hw /* host[B][2] */);
+
+IVX_API int ivx_backproject_scenes_nchw(const float *feat, const int64_t *feat_strides /* host[5] */,
+                                        int n_scenes, int n_views, int n_channels,
+                                        const int32_t *hw /* host[B][2] */, const float *proj,
+                                        const float *points, const ivx_grid *grid,
+                                        const float *new_origin /* host[B][3] */, int64_t n_points,
+                                        void *volume, const int64_t *vol_strides /* host[3] */,
+                                        int vol_dtype, int reduce, uint8_t *valid, int32_t *count,
+                                        void *workspace, int64_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
