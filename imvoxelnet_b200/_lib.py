@@ -43,6 +43,8 @@ PROTOTYPES = {
                                     _GridP, _f32p, c_int64, c_void_p, _i64p, c_int, c_int, c_void_p,
                                     c_void_p, c_void_p, c_int64, c_void_p],
 }
+PROTOTYPES["ivx_backproject_scenes_nchw_noalloc"] = PROTOTYPES["ivx_backproject_scenes_nchw"][:17] + [c_void_p]
+IVX_NOALLOC_SCRATCH_BYTES = 32 * 1024 * 1024
 RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64}
 
 _lib = None

@@ -28,6 +28,8 @@
 // so that nvcc can neither contract nor reassociate it.
 #include <cuda_bf16.h>
 
+#include <mutex>
+
 #include "ivx_common.cuh"
 
 namespace ivx {
@@ -827,4 +829,72 @@ extern "C" int ivx_backproject_scenes_nchw(const float *feat, const int64_t *fea
     return ivx_backproject_scenes(ws, ws_strides, n_scenes, n_views, n_channels, hw, proj, points,
                                   grid, new_origin, n_points, volume, vol_strides, vol_dtype, reduce,
                                   valid, count, stream);
+}
+
+// ---------------------------------------------------------------------------
+// Allocation-free variant of ivx_backproject_scenes_nchw.
+//
+// Some users of this library run where device memory cannot be requested at
+// call time: a plugin inside a host application that has already handed all
+// GPU memory to its own pool (so cudaMalloc fails although the pool has room),
+// or a serving / real-time thread that must not take the driver's allocation
+// lock or suffer the device-wide synchronisation cudaMalloc and cudaFree imply.
+// For them the channels-last copy of the maps lives in the fixed array below
+// instead of a caller-provided workspace.  Every GPU that loads the library
+// holds these IVX_NOALLOC_SCRATCH_BYTES until the process exits.
+//
+// `g_noalloc_scratch` is a device symbol: in host code its name is only a
+// stand-in, so the device address is looked up with cudaGetSymbolAddress,
+// once per device and with that device current, and cached.
+// ---------------------------------------------------------------------------
+static __device__ __align__(256) float g_noalloc_scratch[IVX_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mutex;
+float *g_noalloc_address[kMaxDevices] = {nullptr};
+
+// Device address of the scratch array on the current device (set-up on first use).
+int noalloc_scratch_address(float **out) {
+    int device = -1;
+    int rc = check_cuda(cudaGetDevice(&device), "cudaGetDevice");
+    if (rc != IVX_OK) return rc;
+    if (device < 0 || device >= kMaxDevices)
+        return fail(IVX_ERR_UNSUPPORTED, "device ordinal %d is beyond the %d this build tracks", device,
+                    kMaxDevices);
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (g_noalloc_address[device] == nullptr) {
+        void *address = nullptr;
+        rc = check_cuda(cudaGetSymbolAddress(&address, g_noalloc_scratch),
+                        "cudaGetSymbolAddress(built-in scratch)");
+        if (rc != IVX_OK) return rc;
+        g_noalloc_address[device] = static_cast<float *>(address);
+    }
+    *out = g_noalloc_address[device];
+    return IVX_OK;
+}
+}  // namespace
+
+extern "C" int ivx_backproject_scenes_nchw_noalloc(
+    const float *feat, const int64_t *feat_strides, int n_scenes, int n_views, int n_channels,
+    const int32_t *hw, const float *proj, const float *points, const ivx_grid *grid,
+    const float *new_origin, int64_t n_points, void *volume, const int64_t *vol_strides, int vol_dtype,
+    int reduce, uint8_t *valid, int32_t *count, void *stream) {
+    IVX_REQUIRE(hw != nullptr && n_scenes > 0 && n_views > 0 && n_channels > 0,
+                "hw must be given and sizes must be positive");
+    const int64_t need = ivx_backproject_nchw_workspace_bytes(n_scenes, n_views, n_channels, hw);
+    if (need > (int64_t)IVX_NOALLOC_SCRATCH_BYTES)
+        return fail(IVX_ERR_UNSUPPORTED,
+                    "these maps need %lld bytes of scratch but the built-in scratch holds %lld: split "
+                    "the batch, or call ivx_backproject_scenes_nchw with a workspace of your own",
+                    (long long)need, (long long)IVX_NOALLOC_SCRATCH_BYTES);
+    float *scratch = nullptr;
+    int rc = noalloc_scratch_address(&scratch);
+    if (rc != IVX_OK) return rc;
+    // The transpose overwrites every element the gather will read, so nothing
+    // in the shared array has to be cleared between calls.
+    return ivx_backproject_scenes_nchw(feat, feat_strides, n_scenes, n_views, n_channels, hw, proj,
+                                       points, grid, new_origin, n_points, volume, vol_strides,
+                                       vol_dtype, reduce, valid, count, scratch,
+                                       (int64_t)IVX_NOALLOC_SCRATCH_BYTES, stream);
 }

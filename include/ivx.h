@@ -195,6 +195,45 @@ IVX_API int ivx_backproject_scenes_nchw(const float *feat, const int64_t *feat_s
                                         int vol_dtype, int reduce, uint8_t *valid, int32_t *count,
                                         void *workspace, int64_t workspace_bytes, void *stream);
 
+/*
+ * ivx_backproject_scenes_nchw_noalloc -- ivx_backproject_scenes_nchw without a
+ * workspace argument.  It has no counterpart in the reference.
+ *
+ * Who it is for: code that cannot obtain device memory when it calls us -- a
+ * plugin whose host application has given all GPU memory to its own pool
+ * (cudaMalloc then fails even though that pool has room), or a serving /
+ * real-time thread that may not take the driver's allocation lock nor trigger
+ * the device-wide synchronisation that cudaMalloc and cudaFree bring.  The
+ * function calls no cudaMalloc / cudaFree and no allocating library routine;
+ * inputs and outputs are still the caller's buffers.
+ *
+ * The channels-last copy of the maps goes to a fixed array inside the library
+ * of IVX_NOALLOC_SCRATCH_BYTES (32 MiB), which every GPU that loads the
+ * library keeps until the process exits.  Requests that need more
+ * (ivx_backproject_nchw_workspace_bytes(...) > IVX_NOALLOC_SCRATCH_BYTES) are
+ * refused with IVX_ERR_UNSUPPORTED and nothing is launched.
+ *
+ * First call on each device: the address of the array on that device is
+ * looked up (with that device current) and remembered; make this first call
+ * before starting any stream capture on that device.
+ *
+ * All calls on one device share the array and it keeps what the last call
+ * left there.  Nothing needs clearing (each call overwrites every element it
+ * later reads), but two calls that overlap on the GPU -- different streams, or
+ * different host threads without ordering -- race on it: keep calls on one
+ * device ordered, e.g. on a single stream.
+ *
+ * Arguments and results as ivx_backproject_scenes_nchw.
+ */
+#define IVX_NOALLOC_SCRATCH_BYTES (32 * 1024 * 1024)
+
+IVX_API int ivx_backproject_scenes_nchw_noalloc(
+    const float *feat, const int64_t *feat_strides /* host[5] */, int n_scenes, int n_views,
+    int n_channels, const int32_t *hw /* host[B][2] */, const float *proj, const float *points,
+    const ivx_grid *grid, const float *new_origin /* host[B][3] */, int64_t n_points, void *volume,
+    const int64_t *vol_strides /* host[3] */, int vol_dtype, int reduce, uint8_t *valid,
+    int32_t *count, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
