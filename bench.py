@@ -185,7 +185,7 @@ def algorithmic_bytes(sc, P, origin, device):
 
 def run_ours(args):
     import torch.distributed as dist
-    from imvoxelnet_b200 import _lib, ops
+    from imvoxelnet_b200 import _lib, ops, sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -225,17 +225,13 @@ def run_ours(args):
     P_dev = Pb.to(dev)
     hws = [(h, w)] * batch
     origins = [origin] * batch
-    reduce_mode = "partial" if view_sharded else "mean"
 
     def step(i):
-        out = ops.backproject_scenes(dev_sets[i % n_sets], hws, P_dev, sc.n_voxels, sc.voxel_size,
-                                     origins, reduce=reduce_mode)
         if view_sharded:
-            s, _, c = out
-            dist.all_reduce(s)
-            dist.all_reduce(c)
-            return ops.finalize_mean(s, c)
-        return out
+            return sharding.backproject_scenes_view_sharded(
+                dev_sets[i % n_sets], hws, P_dev, sc.n_voxels, sc.voxel_size, origins)
+        return ops.backproject_scenes(dev_sets[i % n_sets], hws, P_dev, sc.n_voxels, sc.voxel_size,
+                                      origins)
 
     def barrier():
         if world > 1:
@@ -331,13 +327,11 @@ def run_ours(args):
     def e2e_step():
         feats = host_pinned.to(dev, non_blocking=True)
         pd = P_pinned.to(dev, non_blocking=True)
-        out = ops.backproject_scenes(feats, hws, pd, sc.n_voxels, sc.voxel_size, origins,
-                                     reduce=reduce_mode)
         if view_sharded:
-            s, _, c = out
-            dist.all_reduce(s)
-            dist.all_reduce(c)
-            out = ops.finalize_mean(s, c)
+            out = sharding.backproject_scenes_view_sharded(feats, hws, pd, sc.n_voxels,
+                                                           sc.voxel_size, origins)
+        else:
+            out = ops.backproject_scenes(feats, hws, pd, sc.n_voxels, sc.voxel_size, origins)
         vol_host.copy_(out[0], non_blocking=True)
         val_host.copy_(out[1], non_blocking=True)
 
