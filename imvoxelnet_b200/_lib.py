@@ -26,6 +26,20 @@ class Grid(ctypes.Structure):
 
 _GridP = ctypes.POINTER(Grid)
 
+
+class ConvParams(ctypes.Structure):
+    """``ivx_conv3d_params`` of include/ivx.h."""
+    _fields_ = [("batch", ctypes.c_int32), ("c_in", ctypes.c_int32), ("c_out", ctypes.c_int32),
+                ("in_dims", ctypes.c_int32 * 3), ("out_dims", ctypes.c_int32 * 3),
+                ("kernel", ctypes.c_int32 * 3), ("stride", ctypes.c_int32 * 3),
+                ("pad", ctypes.c_int32 * 3), ("transposed", ctypes.c_int32),
+                ("relu", ctypes.c_int32), ("residual_after_act", ctypes.c_int32),
+                ("post_scale", ctypes.c_float), ("in_dtype", ctypes.c_int32),
+                ("out_dtype", ctypes.c_int32)]
+
+
+_ConvP = ctypes.POINTER(ConvParams)
+
 # name -> argtypes, exactly the prototypes of include/ivx.h
 PROTOTYPES = {
     "ivx_project_indices": [c_void_p, _GridP, _f32p, c_int64, c_void_p, c_int, c_int, c_int,
@@ -45,6 +59,9 @@ PROTOTYPES = {
 }
 PROTOTYPES["ivx_backproject_scenes_nchw_noalloc"] = PROTOTYPES["ivx_backproject_scenes_nchw"][:17] + [c_void_p]
 IVX_NOALLOC_SCRATCH_BYTES = 32 * 1024 * 1024
+PROTOTYPES["ivx_conv3d_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                  c_void_p]
+PROTOTYPES["ivx_upsample2x_trilinear_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_int, c_void_p]
 RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64}
 
 _lib = None

@@ -1,0 +1,138 @@
+"""Fused convolution layers of the 3D necks on top of the C-ABI kernels.
+
+A ``FusedConv`` wraps the parameter-holding ``nn.Conv3d`` /
+``nn.ConvTranspose3d`` (+ ``nn.BatchNorm3d``) modules of a reference block
+(mmdet3d/models/necks/imvoxelnet.py) and runs them as ONE kernel in eval mode:
+BN folded into scale/shift, bias folded into shift, residual / ReLU / the
+decoder's ``(x + y) / 2`` in the epilogue.  Activations are channels-last
+``[B, X, Y, Z, C]`` tensors between layers.
+"""
+import torch
+from torch import nn
+
+from . import _lib
+
+__all__ = ["FusedConv", "upsample2x_trilinear", "to_ndhwc", "from_ndhwc", "launch_count"]
+
+_launches = 0
+_DT = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}
+
+
+def launch_count():
+    return _launches
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def to_ndhwc(x):
+    """Logical [B,C,X,Y,Z] tensor -> dense [B,X,Y,Z,C] (free for channels_last_3d input)."""
+    if not x.is_cuda:
+        raise _lib.IvxError("the 3D-neck kernels need CUDA tensors: there is no CPU implementation")
+    return x.permute(0, 2, 3, 4, 1).contiguous()
+
+
+def from_ndhwc(y):
+    """Dense [B,X,Y,Z,C] -> logical [B,C,X,Y,Z] view (channels_last_3d strides)."""
+    return y.permute(0, 4, 1, 2, 3)
+
+
+def _triple(v):
+    return tuple(v) if isinstance(v, (tuple, list)) else (v, v, v)
+
+
+class FusedConv:
+    """conv (+ BN) (+ ReLU) as one launch; parameters stay in the nn.Modules."""
+
+    def __init__(self, conv, bn=None, relu=False):
+        self.conv, self.bn, self.relu = conv, bn, relu
+        self.transposed = isinstance(conv, nn.ConvTranspose3d)
+        if not self.transposed:
+            assert tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1
+        self._packed = None
+
+    # ---- parameter packing (cached until a parameter or buffer changes) ----
+    def _key(self, device):
+        tensors = [self.conv.weight, self.conv.bias]
+        if self.bn is not None:
+            tensors += [self.bn.weight, self.bn.bias, self.bn.running_mean, self.bn.running_var]
+        return (str(device),) + tuple((t.data_ptr(), t._version) if t is not None else None
+                                      for t in tensors)
+
+    def packed(self, device):
+        key = self._key(device)
+        if self._packed is None or self._packed[0] != key:
+            with torch.no_grad():
+                w = self.conv.weight.detach().to(device=device, dtype=torch.float32)
+                if self.transposed:       # [Cin, Cout, kx, ky, kz] -> [Cin][taps][Cout]
+                    wp = w.permute(0, 2, 3, 4, 1).contiguous()
+                else:                     # [Cout, Cin, kx, ky, kz] -> [taps][Cin][Cout]
+                    wp = w.permute(2, 3, 4, 1, 0).contiguous()
+                scale = shift = None
+                bias = self.conv.bias
+                if self.bn is not None:
+                    bn = self.bn
+                    scale = (bn.weight / torch.sqrt(bn.running_var + bn.eps)).to(device, torch.float32)
+                    shift = (bn.bias - bn.running_mean * scale.to(bn.bias.device)).to(device, torch.float32)
+                    if bias is not None:
+                        shift = shift + bias.to(device, torch.float32) * scale
+                    scale, shift = scale.contiguous(), shift.contiguous()
+                elif bias is not None:
+                    shift = bias.detach().to(device, torch.float32).contiguous()
+            self._packed = (key, wp, scale, shift)
+        return self._packed[1:]
+
+    def out_dims(self, in_dims):
+        k, s = _triple(self.conv.kernel_size), _triple(self.conv.stride)
+        p = _triple(self.conv.padding)
+        if self.transposed:
+            return tuple(i * st for i, st in zip(in_dims, s))
+        return tuple((i + 2 * pd - kk) // st + 1 for i, pd, kk, st in zip(in_dims, p, k, s))
+
+    def __call__(self, x, residual=None, residual_after_act=False, post_scale=1.0, out_dtype=None):
+        """x: [B,X,Y,Z,Cin] dense CUDA tensor -> [B,X',Y',Z',Cout]."""
+        global _launches
+        if not x.is_cuda:
+            raise _lib.IvxError("the 3D-neck kernels need CUDA tensors: there is no CPU implementation")
+        assert x.is_contiguous() and x.dim() == 5
+        b, in_dims, cin = x.shape[0], tuple(x.shape[1:4]), x.shape[4]
+        cout = self.conv.out_channels
+        assert cin == self.conv.in_channels, (cin, self.conv.in_channels)
+        od = self.out_dims(in_dims)
+        out_dtype = out_dtype or x.dtype
+        y = torch.empty((b,) + od + (cout,), dtype=out_dtype, device=x.device)
+        wp, scale, shift = self.packed(x.device)
+        p = _lib.ConvParams()
+        p.batch, p.c_in, p.c_out = b, cin, cout
+        k, s, pd = _triple(self.conv.kernel_size), _triple(self.conv.stride), _triple(self.conv.padding)
+        for d in range(3):
+            p.in_dims[d], p.out_dims[d] = in_dims[d], od[d]
+            p.kernel[d], p.stride[d], p.pad[d] = k[d], s[d], pd[d]
+        p.transposed, p.relu = int(self.transposed), int(self.relu)
+        p.residual_after_act, p.post_scale = int(residual_after_act), float(post_scale)
+        p.in_dtype, p.out_dtype = _DT[x.dtype], _DT[out_dtype]
+        if residual is not None:
+            assert residual.shape == y.shape and residual.dtype == y.dtype and residual.is_contiguous()
+        with torch.cuda.device(x.device):
+            _lib.check(_lib.lib().ivx_conv3d_ndhwc(
+                p, x.data_ptr(), wp.data_ptr(), scale.data_ptr() if scale is not None else None,
+                shift.data_ptr() if shift is not None else None,
+                residual.data_ptr() if residual is not None else None, y.data_ptr(), _stream()),
+                "ivx_conv3d_ndhwc")
+        _launches += 1
+        return y
+
+
+def upsample2x_trilinear(x):
+    """F.interpolate(scale_factor=2, mode='trilinear', align_corners=False) on [B,X,Y,Z,C]."""
+    global _launches
+    assert x.is_cuda and x.is_contiguous() and x.dim() == 5
+    b, xs, ys, zs, c = x.shape
+    y = torch.empty((b, 2 * xs, 2 * ys, 2 * zs, c), dtype=x.dtype, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().ivx_upsample2x_trilinear_ndhwc(
+            x.data_ptr(), y.data_ptr(), b, c, _lib.i32([xs, ys, zs]), _DT[x.dtype], _stream()),
+            "ivx_upsample2x_trilinear_ndhwc")
+    _launches += 1
+    return y

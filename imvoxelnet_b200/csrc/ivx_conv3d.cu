@@ -1,0 +1,314 @@
+// 3D-neck building blocks on CUDA cores, channels-last (NDHWC) activations.
+//
+// The reference's necks (mmdet3d/models/necks/imvoxelnet.py) are stacks of
+// nn.Conv3d / nn.ConvTranspose3d + BatchNorm3d (+ residual) + ReLU and, in
+// the Atlas encoder-decoder, trilinear x2 upsampling.  In eval mode every BN
+// folds into a per-channel scale/shift, so one kernel per conv does
+//     y = post_scale * ( act( conv(x) * scale + shift [+ res] ) [+ res] )
+// This file holds the fp32-accumulating SIMT implicit-GEMM kernel that serves
+// every layer shape (any kernel/stride/pad, 1x1x1, transposed k==s) and is the
+// 1e-5 parity path; the tcgen05 tensor-core kernel for the FLOP-heavy 3x3x3
+// layers lives in ivx_conv3d_tc.cu.
+#include <cuda_bf16.h>
+
+#include "ivx_common.cuh"
+
+namespace ivx {
+
+constexpr int BM = 64;   // output voxels per CTA
+constexpr int BN = 64;   // output channels per CTA
+constexpr int BK = 16;   // input channels per k-step
+
+struct ConvArgs {
+    ivx_conv3d_params p;
+    const void *x;
+    const float *w;      // [taps][c_in][n_cols] fp32, n_cols = c_out (or taps_t * c_out if transposed)
+    const float *scale;  // [c_out] or nullptr (= 1)
+    const float *shift;  // [c_out] or nullptr (= 0)
+    const void *res;     // like y, or nullptr
+    void *y;
+    long long m_total;   // GEMM rows: output voxels (input voxels if transposed)
+    int n_cols;
+    int taps;
+};
+
+template <typename T>
+__device__ __forceinline__ float4 load4(const T *p);
+
+template <>
+__device__ __forceinline__ float4 load4<float>(const float *p) {
+    return __ldg(reinterpret_cast<const float4 *>(p));
+}
+
+template <>
+__device__ __forceinline__ float4 load4<__nv_bfloat16>(const __nv_bfloat16 *p) {
+    const uint2 u = __ldg(reinterpret_cast<const uint2 *>(p));
+    const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162 *>(&u.x);
+    const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162 *>(&u.y);
+    const float2 a = __bfloat1622float2(lo), b = __bfloat1622float2(hi);
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+
+template <typename T>
+__device__ __forceinline__ void store4v(T *p, float4 v);
+
+template <>
+__device__ __forceinline__ void store4v<float>(float *p, float4 v) {
+    *reinterpret_cast<float4 *>(p) = v;
+}
+
+template <>
+__device__ __forceinline__ void store4v<__nv_bfloat16>(__nv_bfloat16 *p, float4 v) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 u;
+    u.x = *reinterpret_cast<unsigned *>(&lo);
+    u.y = *reinterpret_cast<unsigned *>(&hi);
+    *reinterpret_cast<uint2 *>(p) = u;
+}
+
+// GEMM row -> (batch, x, y, z) of the row's voxel grid (dims d)
+__device__ __forceinline__ void decode_row(long long m, const int32_t d[3], int &b, int &x, int &y,
+                                           int &z) {
+    z = (int)(m % d[2]);
+    long long t = m / d[2];
+    y = (int)(t % d[1]);
+    t /= d[1];
+    x = (int)(t % d[0]);
+    b = (int)(t / d[0]);
+}
+
+template <typename TIn, typename TOut>
+__global__ void __launch_bounds__(256) conv3d_simt_kernel(const __grid_constant__ ConvArgs a) {
+    __shared__ float As[BK][BM + 4];
+    __shared__ float Bs[BK][BN];
+    const ivx_conv3d_params &p = a.p;
+    const int tid = threadIdx.x;
+    const long long m0 = (long long)blockIdx.x * BM;
+    const int n0 = blockIdx.y * BN;
+
+    // the row this thread stages into As (4 consecutive input channels of it)
+    const int arow = tid >> 2, ak = (tid & 3) * 4;
+    const long long am = m0 + arow;
+    const bool arow_ok = am < a.m_total;
+    int ab = 0, ax = 0, ay = 0, az = 0;
+    const int32_t *row_dims = p.transposed ? p.in_dims : p.out_dims;
+    if (arow_ok) decode_row(am, row_dims, ab, ax, ay, az);
+    // the weight slice this thread stages into Bs
+    const int bk = tid >> 4, bc = (tid & 15) * 4;
+
+    const int ty = tid >> 4, tx = tid & 15;  // 4x4 micro-tile: rows ty*4.., cols tx*4..
+    float acc[4][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    const TIn *x = static_cast<const TIn *>(a.x);
+    for (int tap = 0; tap < a.taps; ++tap) {
+        long long in_off = -1;
+        if (arow_ok) {
+            if (p.transposed) {
+                in_off = (((long long)ab * p.in_dims[0] + ax) * p.in_dims[1] + ay) * p.in_dims[2] + az;
+            } else {
+                const int kz = tap % p.kernel[2], t2 = tap / p.kernel[2];
+                const int ky = t2 % p.kernel[1], kx = t2 / p.kernel[1];
+                const int xi = ax * p.stride[0] - p.pad[0] + kx;
+                const int yi = ay * p.stride[1] - p.pad[1] + ky;
+                const int zi = az * p.stride[2] - p.pad[2] + kz;
+                if (xi >= 0 && xi < p.in_dims[0] && yi >= 0 && yi < p.in_dims[1] && zi >= 0 &&
+                    zi < p.in_dims[2])
+                    in_off = (((long long)ab * p.in_dims[0] + xi) * p.in_dims[1] + yi) * p.in_dims[2] + zi;
+            }
+        }
+        const float *wt = a.w + (long long)tap * p.c_in * a.n_cols;
+        for (int c0 = 0; c0 < p.c_in; c0 += BK) {
+            float4 av = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (in_off >= 0 && c0 + ak < p.c_in) av = load4<TIn>(x + in_off * p.c_in + c0 + ak);
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c0 + bk < p.c_in && n0 + bc < a.n_cols)
+                bv = __ldg(reinterpret_cast<const float4 *>(wt + (long long)(c0 + bk) * a.n_cols + n0 + bc));
+            __syncthreads();  // previous k-step fully consumed
+            As[ak + 0][arow] = av.x;
+            As[ak + 1][arow] = av.y;
+            As[ak + 2][arow] = av.z;
+            As[ak + 3][arow] = av.w;
+            *reinterpret_cast<float4 *>(&Bs[bk][bc]) = bv;
+            __syncthreads();
+#pragma unroll
+            for (int k = 0; k < BK; ++k) {
+                const float4 ar = *reinterpret_cast<const float4 *>(&As[k][ty * 4]);
+                const float4 br = *reinterpret_cast<const float4 *>(&Bs[k][tx * 4]);
+                const float av4[4] = {ar.x, ar.y, ar.z, ar.w};
+                const float bv4[4] = {br.x, br.y, br.z, br.w};
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av4[i], bv4[j], acc[i][j]);
+            }
+        }
+    }
+
+    // epilogue: folded BN, residual, ReLU, scale; 4 consecutive channels per store
+    const int col = n0 + tx * 4;
+    if (col >= a.n_cols) return;
+    int co = col, ttap = 0;
+    if (p.transposed) {
+        ttap = col / p.c_out;
+        co = col - ttap * p.c_out;
+    }
+    float4 sc = make_float4(1.f, 1.f, 1.f, 1.f), sh = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (a.scale) sc = __ldg(reinterpret_cast<const float4 *>(a.scale + co));
+    if (a.shift) sh = __ldg(reinterpret_cast<const float4 *>(a.shift + co));
+    TOut *y = static_cast<TOut *>(a.y);
+    const TOut *res = static_cast<const TOut *>(a.res);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const long long m = m0 + ty * 4 + i;
+        if (m >= a.m_total) break;
+        long long ovox = m;
+        if (p.transposed) {
+            int b, xi, yi, zi;
+            decode_row(m, p.in_dims, b, xi, yi, zi);
+            const int kz = ttap % p.kernel[2], t2 = ttap / p.kernel[2];
+            const int ky = t2 % p.kernel[1], kx = t2 / p.kernel[1];
+            ovox = (((long long)b * p.out_dims[0] + xi * p.stride[0] + kx) * p.out_dims[1] +
+                    yi * p.stride[1] + ky) * p.out_dims[2] + zi * p.stride[2] + kz;
+        }
+        float4 v = make_float4(fmaf(acc[i][0], sc.x, sh.x), fmaf(acc[i][1], sc.y, sh.y),
+                               fmaf(acc[i][2], sc.z, sh.z), fmaf(acc[i][3], sc.w, sh.w));
+        float4 r = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (res) r = load4<TOut>(res + ovox * p.c_out + co);
+        if (res && !p.residual_after_act) v.x += r.x, v.y += r.y, v.z += r.z, v.w += r.w;
+        if (p.relu) v.x = fmaxf(v.x, 0.f), v.y = fmaxf(v.y, 0.f), v.z = fmaxf(v.z, 0.f), v.w = fmaxf(v.w, 0.f);
+        if (res && p.residual_after_act) v.x += r.x, v.y += r.y, v.z += r.z, v.w += r.w;
+        if (p.post_scale != 1.f) v.x *= p.post_scale, v.y *= p.post_scale, v.z *= p.post_scale, v.w *= p.post_scale;
+        store4v<TOut>(y + ovox * p.c_out + co, v);
+    }
+}
+
+// F.interpolate(scale_factor=2, mode='trilinear', align_corners=False) on NDHWC
+// (necks/imvoxelnet.py:359): source index (dst + 0.5) / 2 - 0.5 clamped at 0,
+// i.e. weights 0.25 / 0.75 with edge replication, combined in ATen's order.
+template <typename T>
+__global__ void __launch_bounds__(256) upsample2x_trilinear_kernel(
+    const T *__restrict__ x, T *__restrict__ y, int B, int X, int Y, int Z, int C4) {
+    const long long total = (long long)B * (2 * X) * (2 * Y) * (2 * Z) * C4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const int c4 = (int)(i % C4);
+        long long t = i / C4;
+        const int zo = (int)(t % (2 * Z));
+        t /= 2 * Z;
+        const int yo = (int)(t % (2 * Y));
+        t /= 2 * Y;
+        const int xo = (int)(t % (2 * X));
+        const int b = (int)(t / (2 * X));
+        int i0[3], i1[3];
+        float l1[3];
+        const int o[3] = {xo, yo, zo}, n[3] = {X, Y, Z};
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            float s = 0.5f * ((float)o[d] + 0.5f) - 0.5f;
+            s = s < 0.f ? 0.f : s;
+            i0[d] = (int)s;
+            i1[d] = i0[d] + (i0[d] < n[d] - 1 ? 1 : 0);
+            l1[d] = s - (float)i0[d];
+        }
+        auto at = [&](int xi, int yi, int zi) {
+            return load4<T>(x + ((((long long)b * X + xi) * Y + yi) * Z + zi) * (C4 * 4ll) + c4 * 4);
+        };
+        auto lerp = [](float4 p, float4 q, float w0, float w1) {
+            return make_float4(w0 * p.x + w1 * q.x, w0 * p.y + w1 * q.y, w0 * p.z + w1 * q.z,
+                               w0 * p.w + w1 * q.w);
+        };
+        const float x0 = 1.f - l1[0], y0 = 1.f - l1[1], z0 = 1.f - l1[2];
+        const float4 a00 = lerp(at(i0[0], i0[1], i0[2]), at(i0[0], i0[1], i1[2]), z0, l1[2]);
+        const float4 a01 = lerp(at(i0[0], i1[1], i0[2]), at(i0[0], i1[1], i1[2]), z0, l1[2]);
+        const float4 a10 = lerp(at(i1[0], i0[1], i0[2]), at(i1[0], i0[1], i1[2]), z0, l1[2]);
+        const float4 a11 = lerp(at(i1[0], i1[1], i0[2]), at(i1[0], i1[1], i1[2]), z0, l1[2]);
+        const float4 v = lerp(lerp(a00, a01, y0, l1[1]), lerp(a10, a11, y0, l1[1]), x0, l1[0]);
+        store4v<T>(y + i * 4, v);
+    }
+}
+
+}  // namespace ivx
+
+using namespace ivx;
+
+static int validate_conv(const ivx_conv3d_params *p) {
+    IVX_REQUIRE(p != nullptr, "NULL params");
+    IVX_REQUIRE(p->batch > 0 && p->c_in > 0 && p->c_out > 0, "batch/c_in/c_out must be positive");
+    IVX_REQUIRE(p->c_in % 4 == 0 && p->c_out % 4 == 0, "channel counts must be multiples of 4");
+    for (int d = 0; d < 3; ++d) {
+        IVX_REQUIRE(p->in_dims[d] > 0 && p->out_dims[d] > 0 && p->kernel[d] > 0 && p->stride[d] > 0 &&
+                        p->pad[d] >= 0,
+                    "bad geometry on axis %d", d);
+        if (p->transposed) {
+            IVX_REQUIRE(p->kernel[d] == p->stride[d] && p->pad[d] == 0 &&
+                            p->out_dims[d] == p->in_dims[d] * p->stride[d],
+                        "transposed convolutions need kernel == stride, pad 0 (axis %d)", d);
+        } else {
+            const int expect = (p->in_dims[d] + 2 * p->pad[d] - p->kernel[d]) / p->stride[d] + 1;
+            IVX_REQUIRE(expect == p->out_dims[d], "axis %d: out_dims %d, expected %d", d, p->out_dims[d],
+                        expect);
+        }
+    }
+    IVX_REQUIRE((p->in_dtype == IVX_F32 || p->in_dtype == IVX_BF16) &&
+                    (p->out_dtype == IVX_F32 || p->out_dtype == IVX_BF16),
+                "unknown dtype");
+    return IVX_OK;
+}
+
+extern "C" int ivx_conv3d_ndhwc(const ivx_conv3d_params *params, const void *x, const float *weight,
+                                const float *scale, const float *shift, const void *residual, void *y,
+                                void *stream) {
+    int rc = validate_conv(params);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(x && weight && y, "NULL argument");
+    ConvArgs a;
+    a.p = *params;
+    a.x = x, a.w = weight, a.scale = scale, a.shift = shift, a.res = residual, a.y = y;
+    const ivx_conv3d_params &p = a.p;
+    const int ktaps = p.kernel[0] * p.kernel[1] * p.kernel[2];
+    const int32_t *rd = p.transposed ? p.in_dims : p.out_dims;
+    a.m_total = (long long)p.batch * rd[0] * rd[1] * rd[2];
+    a.n_cols = p.transposed ? ktaps * p.c_out : p.c_out;
+    a.taps = p.transposed ? 1 : ktaps;
+    const long long gx = (a.m_total + BM - 1) / BM;
+    IVX_REQUIRE(gx < (1ll << 31), "too many output voxels");
+    dim3 grid((unsigned)gx, (unsigned)((a.n_cols + BN - 1) / BN));
+    cudaStream_t s = (cudaStream_t)stream;
+    if (p.in_dtype == IVX_F32 && p.out_dtype == IVX_F32)
+        conv3d_simt_kernel<float, float><<<grid, 256, 0, s>>>(a);
+    else if (p.in_dtype == IVX_BF16 && p.out_dtype == IVX_BF16)
+        conv3d_simt_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, s>>>(a);
+    else if (p.in_dtype == IVX_F32 && p.out_dtype == IVX_BF16)
+        conv3d_simt_kernel<float, __nv_bfloat16><<<grid, 256, 0, s>>>(a);
+    else
+        conv3d_simt_kernel<__nv_bfloat16, float><<<grid, 256, 0, s>>>(a);
+    IVX_CHECK_LAUNCH("conv3d launch");
+    return IVX_OK;
+}
+
+extern "C" int ivx_upsample2x_trilinear_ndhwc(const void *x, void *y, int batch, int n_channels,
+                                              const int32_t *in_dims, int dtype, void *stream) {
+    IVX_REQUIRE(x && y && in_dims, "NULL argument");
+    IVX_REQUIRE(batch > 0 && n_channels > 0 && n_channels % 4 == 0, "channels must be a multiple of 4");
+    IVX_REQUIRE(in_dims[0] > 0 && in_dims[1] > 0 && in_dims[2] > 0, "bad dims");
+    IVX_REQUIRE(dtype == IVX_F32 || dtype == IVX_BF16, "unknown dtype");
+    const long long total = 8ll * batch * in_dims[0] * in_dims[1] * in_dims[2] * (n_channels / 4);
+    long long gx = (total + 255) / 256;
+    if (gx > kNumSMs * 32) gx = kNumSMs * 32;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (dtype == IVX_F32)
+        upsample2x_trilinear_kernel<float><<<(unsigned)gx, 256, 0, s>>>(
+            static_cast<const float *>(x), static_cast<float *>(y), batch, in_dims[0], in_dims[1],
+            in_dims[2], n_channels / 4);
+    else
+        upsample2x_trilinear_kernel<__nv_bfloat16><<<(unsigned)gx, 256, 0, s>>>(
+            static_cast<const __nv_bfloat16 *>(x), static_cast<__nv_bfloat16 *>(y), batch, in_dims[0],
+            in_dims[1], in_dims[2], n_channels / 4);
+    IVX_CHECK_LAUNCH("upsample launch");
+    return IVX_OK;
+}

@@ -234,6 +234,57 @@ IVX_API int ivx_backproject_scenes_nchw_noalloc(
     const int64_t *vol_strides /* host[3] */, int vol_dtype, int reduce, uint8_t *valid,
     int32_t *count, void *stream);
 
+/* ------------------------------ 3D neck ------------------------------ */
+
+/*
+ * One convolution layer of a 3D neck with everything that follows it folded
+ * in.  Replaces an nn.Conv3d / nn.ConvTranspose3d + nn.BatchNorm3d (eval) +
+ * residual add + nn.ReLU group of mmdet3d/models/necks/imvoxelnet.py (e.g.
+ * BasicBlock3d.forward :212-230, BasicBlock3dV2.forward :248-260, _make_block
+ * :48-53, _make_up_block :56-64, _get_conv :109-114, ConditionalProjection
+ * :289-294 followed by the (x + y) / 2 of :367):
+ *
+ *   v = conv(x) * scale + shift            (BN folded; bias folded into shift)
+ *   if (residual && !residual_after_act) v += residual
+ *   if (relu) v = max(v, 0)
+ *   if (residual &&  residual_after_act) v += residual
+ *   y = v * post_scale
+ *
+ * Activations are channels-last: x is [batch][in_dims X,Y,Z][c_in], y and
+ * residual are [batch][out_dims][c_out], dense.  (kX,kY,kZ) of the reference's
+ * weight [c_out][c_in][kD][kH][kW] correspond to (X,Y,Z) of the volume.
+ */
+typedef struct ivx_conv3d_params {
+    int32_t batch, c_in, c_out;
+    int32_t in_dims[3], out_dims[3];
+    int32_t kernel[3], stride[3], pad[3];
+    int32_t transposed;         /* 1: ConvTranspose3d with kernel == stride, pad 0 (:57) */
+    int32_t relu;
+    int32_t residual_after_act;
+    float post_scale;
+    int32_t in_dtype, out_dtype; /* ivx_dtype of x, and of y / residual */
+} ivx_conv3d_params;
+
+/*
+ * ivx_conv3d_ndhwc -- fp32-accumulating CUDA-core implicit GEMM for every layer
+ * shape (the 1e-5 parity path).  weight: fp32, [kX*kY*kZ][c_in][c_out]; for
+ * transposed layers [c_in][kX*kY*kZ][c_out].  scale / shift: fp32 [c_out] or
+ * NULL (1 / 0).  c_in and c_out must be multiples of 4.
+ */
+IVX_API int ivx_conv3d_ndhwc(const ivx_conv3d_params *params, const void *x, const float *weight,
+                             const float *scale, const float *shift, const void *residual, void *y,
+                             void *stream);
+
+/*
+ * ivx_upsample2x_trilinear_ndhwc -- F.interpolate(x, scale_factor=2,
+ * mode='trilinear', align_corners=False) of EncoderDecoder.forward
+ * (necks/imvoxelnet.py:359) on a channels-last [batch][X][Y][Z][C] tensor;
+ * y is [batch][2X][2Y][2Z][C], same dtype.
+ */
+IVX_API int ivx_upsample2x_trilinear_ndhwc(const void *x, void *y, int batch, int n_channels,
+                                           const int32_t *in_dims /* host[3] */, int dtype,
+                                           void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -173,5 +173,33 @@ def main():
     np.savez(os.path.join(HERE, "fullsize_digests.npz"), **dig)
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and "--necks" not in sys.argv:
     main()
+
+
+# --------------------------------------------------------------------------
+# 3D necks: state dict + input + outputs of the reference modules (small sizes)
+# --------------------------------------------------------------------------
+from tests.golden.cases import NECK_CASES  # noqa: E402
+
+
+def make_necks():
+    from oracle import torch_necks
+    _, necks = ref_loader.load()
+    for i, (name, (kw, shape)) in enumerate(NECK_CASES.items()):
+        torch.manual_seed(100 + i)
+        module = getattr(necks, name)(**kw).eval()
+        torch_necks.randomize_norms(module, seed=200 + i)      # non-trivial BN, non-zero bn2.weight
+        x = torch.randn(shape)
+        with torch.no_grad():
+            outs = module(x)
+        blob = {f"sd/{k}": v.numpy() for k, v in module.state_dict().items()}
+        blob["x"] = x.numpy()
+        for j, o in enumerate(outs):
+            blob[f"out{j}"] = o.contiguous().numpy()
+        np.savez(os.path.join(HERE, f"neck_{name}.npz"), **blob)
+        print(name, [tuple(o.shape) for o in outs], sum(v.size for k, v in blob.items() if k.startswith("sd/")), "params")
+
+
+if __name__ == "__main__" and "--necks" in sys.argv:
+    make_necks()

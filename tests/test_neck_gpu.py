@@ -1,0 +1,85 @@
+"""Parity of the CUDA 3D necks with the reference (fp32 mode: 1e-5 relative).
+
+Anchors: golden fixtures produced by the reference's own modules, and the
+torch oracle (pinned to the reference in tests/test_neck_oracle.py) run on
+the GPU in fp32 with TF32 disabled at larger sizes."""
+import numpy as np
+import pytest
+import torch
+
+from imvoxelnet_b200 import necks
+from oracle import torch_necks
+from tests.golden.cases import NECK_CASES
+from tests.util import assert_volume_close, load_golden
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+@pytest.fixture(autouse=True)
+def _no_tf32():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+def _state_dict(g):
+    return {k[3:]: torch.from_numpy(g[k]) for k in g.files if k.startswith("sd/")}
+
+
+@pytest.mark.parametrize("name", sorted(NECK_CASES))
+def test_neck_matches_reference_golden(name):
+    g = load_golden(f"neck_{name}")
+    kw, shape = NECK_CASES[name]
+    m = getattr(necks, name)(**kw).eval()
+    m.load_state_dict(_state_dict(g))
+    m.to(DEV)
+    with torch.no_grad():
+        outs = m(torch.from_numpy(g["x"]).to(DEV))
+    n_out = sum(1 for k in g.files if k.startswith("out"))
+    assert len(outs) == n_out
+    for j, o in enumerate(outs):
+        assert o.shape == g[f"out{j}"].shape and o.dtype == torch.float32
+        assert_volume_close(o.cpu().numpy(), g[f"out{j}"])
+
+
+BIGGER = {
+    "FastIndoorImVoxelNeck": (dict(in_channels=64, n_blocks=[1, 1, 1], out_channels=32), (2, 64, 12, 8, 8)),
+    "ImVoxelNeck": (dict(channels=[16, 32, 64, 128], out_channels=16, down_layers=[1, 2, 3, 4],
+                         up_layers=[3, 2, 1], conditional=False), (1, 16, 16, 24, 8)),
+    "KittiImVoxelNeck": (dict(in_channels=64, out_channels=256), (2, 64, 13, 18, 12)),
+    "NuScenesImVoxelNeck": (dict(in_channels=64, out_channels=256), (1, 64, 16, 14, 12)),
+}
+
+
+@pytest.mark.parametrize("name", sorted(BIGGER))
+def test_neck_matches_oracle_at_real_channel_counts(name):
+    kw, shape = BIGGER[name]
+    torch.manual_seed(11)
+    ref = torch_necks.NECKS[name](**kw).eval()
+    torch_necks.randomize_norms(ref, 5)
+    m = getattr(necks, name)(**kw).eval()
+    m.load_state_dict(ref.state_dict())
+    ref.to(DEV), m.to(DEV)
+    x = torch.randn(shape, device=DEV)
+    with torch.no_grad():
+        want = ref(x)
+        got = m(x.contiguous(memory_format=torch.channels_last_3d))   # the layout backproject emits
+    for a, b in zip(got, want):
+        assert a.shape == b.shape
+        assert_volume_close(a.cpu().numpy(), b.cpu().numpy())
+
+
+def test_weights_are_repacked_after_a_state_dict_load():
+    kw, shape = NECK_CASES["KittiImVoxelNeck"]
+    m = necks.KittiImVoxelNeck(**kw).eval().to(DEV)
+    x = torch.randn(shape, device=DEV)
+    with torch.no_grad():
+        a = m(x)[0].clone()
+        g = load_golden("neck_KittiImVoxelNeck")
+        m.load_state_dict(_state_dict(g))
+        b = m(torch.from_numpy(g["x"]).to(DEV))[0]
+    assert_volume_close(b.cpu().numpy(), g["out0"])
+    assert not torch.equal(a, b)
