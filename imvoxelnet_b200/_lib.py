@@ -61,6 +61,7 @@ PROTOTYPES["ivx_backproject_scenes_nchw_noalloc"] = PROTOTYPES["ivx_backproject_
 IVX_NOALLOC_SCRATCH_BYTES = 32 * 1024 * 1024
 PROTOTYPES["ivx_conv3d_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p]
+PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"] = list(PROTOTYPES["ivx_conv3d_ndhwc"])
 PROTOTYPES["ivx_upsample2x_trilinear_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_int, c_void_p]
 RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64}
 

@@ -15,6 +15,8 @@ from . import _lib
 __all__ = ["FusedConv", "upsample2x_trilinear", "to_ndhwc", "from_ndhwc", "launch_count"]
 
 _launches = 0
+#: bf16 layers with c_in, c_out multiples of 64 run on tcgen05; False forces the CUDA-core kernel
+USE_TENSOR_CORES = True
 _DT = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}
 
 
@@ -51,6 +53,7 @@ class FusedConv:
         if not self.transposed:
             assert tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1
         self._packed = None
+        self._packed_tc = None
 
     # ---- parameter packing (cached until a parameter or buffer changes) ----
     def _key(self, device):
@@ -81,7 +84,22 @@ class FusedConv:
                 elif bias is not None:
                     shift = bias.detach().to(device, torch.float32).contiguous()
             self._packed = (key, wp, scale, shift)
+            self._packed_tc = None
         return self._packed[1:]
+
+    def packed_tc(self, device):
+        """bf16 weights [Cout][taps][Cin] for the tensor-core kernel (+ fp32 scale/shift)."""
+        _, scale, shift = self.packed(device)
+        if self._packed_tc is None:
+            with torch.no_grad():
+                w = self.conv.weight.detach().to(device=device, dtype=torch.float32)
+                self._packed_tc = w.permute(0, 2, 3, 4, 1).contiguous().to(torch.bfloat16)
+        return self._packed_tc, scale, shift
+
+    def tc_eligible(self, x, out_dtype):
+        return (not self.transposed and x.dtype == torch.bfloat16 and out_dtype == torch.bfloat16
+                and self.conv.in_channels % 64 == 0 and self.conv.out_channels % 64 == 0
+                and USE_TENSOR_CORES)
 
     def out_dims(self, in_dims):
         k, s = _triple(self.conv.kernel_size), _triple(self.conv.stride)
@@ -114,12 +132,19 @@ class FusedConv:
         p.in_dtype, p.out_dtype = _DT[x.dtype], _DT[out_dtype]
         if residual is not None:
             assert residual.shape == y.shape and residual.dtype == y.dtype and residual.is_contiguous()
+        res_ptr = residual.data_ptr() if residual is not None else None
         with torch.cuda.device(x.device):
-            _lib.check(_lib.lib().ivx_conv3d_ndhwc(
-                p, x.data_ptr(), wp.data_ptr(), scale.data_ptr() if scale is not None else None,
-                shift.data_ptr() if shift is not None else None,
-                residual.data_ptr() if residual is not None else None, y.data_ptr(), _stream()),
-                "ivx_conv3d_ndhwc")
+            if self.tc_eligible(x, out_dtype):
+                wt, scale, shift = self.packed_tc(x.device)
+                _lib.check(_lib.lib().ivx_conv3d_ndhwc_bf16_tc(
+                    p, x.data_ptr(), wt.data_ptr(), scale.data_ptr() if scale is not None else None,
+                    shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(), _stream()),
+                    "ivx_conv3d_ndhwc_bf16_tc")
+            else:
+                _lib.check(_lib.lib().ivx_conv3d_ndhwc(
+                    p, x.data_ptr(), wp.data_ptr(), scale.data_ptr() if scale is not None else None,
+                    shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(), _stream()),
+                    "ivx_conv3d_ndhwc")
         _launches += 1
         return y
 

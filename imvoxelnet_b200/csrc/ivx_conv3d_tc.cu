@@ -1,0 +1,501 @@
+// Tensor-core Conv3d for the 3D necks: implicit GEMM on tcgen05 / TMEM fed by TMA.
+//
+// GEMM view of one layer (channels-last bf16 activations):
+//   M = output voxels, N = c_out, K = kX*kY*kZ * c_in
+//   A[m][(tap, ci)] = x[voxel(m) * stride - pad + tap][ci]   (0 outside the volume)
+//   B[(tap, ci)][n] = w[n][tap][ci]
+// One CTA owns a 128-row tile = a box of (bx, by, bz) output voxels and up to
+// 256 output channels.  For every (tap, 64-channel chunk) k-step the producer
+// thread issues
+//   * one 5-D TMA box load of the activations with the box start shifted by
+//     the tap (and the element strides of the tensor map equal to the conv
+//     stride): zero padding is the TMA's out-of-bounds fill, and the box lands
+//     in shared memory as 128 rows x 128 bytes, 128B-swizzled -- exactly the
+//     K-major operand layout tcgen05.mma expects;
+//   * one 2-D TMA load of the [n][64] weight slice, same layout.
+// A single thread issues tcgen05.mma (M=128, N=c_out tile, K=16, bf16 in, fp32
+// accumulate in TMEM); tcgen05.commit releases the smem stage and, after the
+// last k-step, hands the accumulator to the four epilogue warps, which read
+// it with tcgen05.ld, apply folded BN scale/shift, residual, ReLU, convert to
+// bf16, stage 64-channel slabs in swizzled shared memory and TMA-store them
+// (the store clips partial tiles).  Two accumulators in TMEM (2 x N columns)
+// let the epilogue of tile i overlap the main loop of tile i+1; CTAs are
+// persistent over tiles.
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "ivx_common.cuh"
+
+namespace ivx {
+
+constexpr int TC_THREADS = 192;      // warp 0: TMA, warp 1: MMA, warps 2..5: epilogue
+constexpr int TC_ROWS = 128;         // UMMA M
+constexpr int TC_KCHUNK = 64;        // bf16 channels per k-step = one 128B swizzle row
+constexpr int TC_A_BYTES = TC_ROWS * 128;
+
+struct TcArgs {
+    int c_in, c_out;
+    int n_tile;                 // output channels per CTA tile (<= 256, multiple of 16)
+    int n_splits;               // c_out / n_tile
+    int taps[3], stride[3], pad[3];
+    int out_dims[3], batch;
+    int box[3];                 // output voxels per tile along x, y, z
+    int tiles[3];               // tiles along x, y, z
+    long long n_tiles;          // batch * tiles * n_splits
+    int stages;
+    int relu, residual_after_act;
+    float post_scale;
+    const float *scale, *shift;
+    const __nv_bfloat16 *res;
+};
+
+// ------------------------------ PTX wrappers ------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
+                                            int c1, int c2, int c3, int c4) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
+                                            int c1) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
+        "[%0], [%1, {%3, %4}], [%2];"
+        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
+        : "memory");
+}
+
+__device__ __forceinline__ void tma_store_5d(const CUtensorMap *map, uint32_t src, int c0, int c1, int c2,
+                                             int c3, int c4) {
+    asm volatile(
+        "cp.async.bulk.tensor.5d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
+        ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
+        : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t slot, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot), "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+
+__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
+}
+
+__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+
+// arrives on the mbarrier once every tcgen05.mma issued so far has completed
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
+                 : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
+          "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]),
+          "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]),
+          "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
+
+// K-major operand tile of 128-byte rows, 128B swizzle: 8-row groups 1024 B apart.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);  // start address, 16-byte units
+    d |= (uint64_t)1 << 16;                      // leading byte offset (unused for swizzled K-major)
+    d |= (uint64_t)(1024 >> 4) << 32;            // stride byte offset between 8-row groups
+    d |= (uint64_t)1 << 46;                      // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
+    return d;
+}
+
+// bf16 x bf16 -> fp32, both operands K-major, M = 128
+__device__ __forceinline__ uint32_t umma_idesc(int n) {
+    return (1u << 4)                      // accumulator format F32
+           | (1u << 7) | (1u << 10)       // A, B format BF16
+           | ((uint32_t)(n >> 3) << 17)   // N
+           | ((uint32_t)(TC_ROWS >> 4) << 24);
+}
+
+struct TileCoord {
+    int b, x0, y0, z0, n0;
+};
+
+__device__ __forceinline__ TileCoord decode_tile(const TcArgs &a, long long t) {
+    TileCoord c;
+    c.n0 = (int)(t % a.n_splits) * a.n_tile;
+    t /= a.n_splits;
+    c.z0 = (int)(t % a.tiles[2]) * a.box[2];
+    t /= a.tiles[2];
+    c.y0 = (int)(t % a.tiles[1]) * a.box[1];
+    t /= a.tiles[1];
+    c.x0 = (int)(t % a.tiles[0]) * a.box[0];
+    c.b = (int)(t / a.tiles[0]);
+    return c;
+}
+
+__global__ void __launch_bounds__(TC_THREADS, 1)
+conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                 const __grid_constant__ CUtensorMap map_y, const __grid_constant__ TcArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    // carve-up (all tiles 1024-byte aligned for the 128B swizzle)
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int b_bytes = a.n_tile * 128;
+    const int stage_bytes = TC_A_BYTES + b_bytes;
+    uint8_t *stage_base = smem;
+    uint8_t *slab_base = smem + (size_t)a.stages * stage_bytes;  // 2 output slabs of 128 x 128 B
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + 2 * TC_A_BYTES);
+    uint64_t *full_bar = bars, *empty_bar = bars + a.stages;
+    uint64_t *acc_full = bars + 2 * a.stages, *acc_empty = acc_full + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tmem_cols = a.n_tile <= 16 ? 32 : (a.n_tile <= 32 ? 64 : (a.n_tile <= 64 ? 128 : (a.n_tile <= 128 ? 256 : 512)));
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < a.stages; ++s) {
+            mbar_init(smem_u32(full_bar + s), 1);
+            mbar_init(smem_u32(empty_bar + s), 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(smem_u32(acc_full + i), 1);
+            mbar_init(smem_u32(acc_empty + i), 4);  // one arrive per epilogue warp
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_y) : "memory");
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+    const int acc_stride = tmem_cols / 2;  // columns between the two accumulators
+
+    const int k_chunks = a.c_in / TC_KCHUNK;
+    const int n_taps = a.taps[0] * a.taps[1] * a.taps[2];
+    const int k_steps = n_taps * k_chunks;
+
+    if (warp == 0) {
+        // ------------------------------ TMA producer ------------------------------
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+                const TileCoord tc = decode_tile(a, t);
+                for (int tap = 0; tap < n_taps; ++tap) {
+                    const int kz = tap % a.taps[2], t2 = tap / a.taps[2];
+                    const int ky = t2 % a.taps[1], kx = t2 / a.taps[1];
+                    const int cx = tc.x0 * a.stride[0] - a.pad[0] + kx;
+                    const int cy = tc.y0 * a.stride[1] - a.pad[1] + ky;
+                    const int cz = tc.z0 * a.stride[2] - a.pad[2] + kz;
+                    for (int kc = 0; kc < k_chunks; ++kc) {
+                        mbar_wait(smem_u32(empty_bar + stage), phase ^ 1);
+                        const uint32_t bar = smem_u32(full_bar + stage);
+                        const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
+                        mbar_expect_tx(bar, (uint32_t)(a.box[0] * a.box[1] * a.box[2] * 128 + b_bytes));
+                        tma_load_5d(sa, &map_x, bar, kc * TC_KCHUNK, cz, cy, cx, tc.b);
+                        tma_load_2d(sa + TC_A_BYTES, &map_w, bar, tap * a.c_in + kc * TC_KCHUNK, tc.n0);
+                        if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------ MMA issuer ------------------------------
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc(a.n_tile);
+            uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
+            for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+                mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);  // epilogue drained this accumulator
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + acc * acc_stride;
+                for (int ks = 0; ks < k_steps; ++ks) {
+                    mbar_wait(smem_u32(full_bar + stage), phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TC_A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < TC_KCHUNK / 16; ++k)  // +32 bytes per K=16 slice inside the swizzle row
+                        umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+                    umma_commit(smem_u32(empty_bar + stage));  // frees the smem stage when the MMAs retire
+                    if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
+                }
+                umma_commit(smem_u32(acc_full + acc));  // accumulator complete
+                if (++acc == 2) acc = 0, acc_phase ^= 1;
+            }
+        }
+    } else {
+        // ------------------------------ epilogue (4 warps) ------------------------------
+        const int q = warp & 3;             // TMEM lane quarter this warp may read
+        const int row = q * 32 + lane;      // tile row = accumulator lane
+        const int box_rows = a.box[0] * a.box[1] * a.box[2];
+        const int iz = row % a.box[2], iy = (row / a.box[2]) % a.box[1], ix = row / (a.box[2] * a.box[1]);
+        const bool epi_leader = (warp == 2 && lane == 0);
+        uint32_t acc = 0, acc_phase = 0;
+        int slab = 0;
+        for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+            const TileCoord tc = decode_tile(a, t);
+            const int ox = tc.x0 + ix, oy = tc.y0 + iy, oz = tc.z0 + iz;
+            const bool row_ok = row < box_rows && ox < a.out_dims[0] && oy < a.out_dims[1] && oz < a.out_dims[2];
+            const long long ovox = (((long long)tc.b * a.out_dims[0] + ox) * a.out_dims[1] + oy) * a.out_dims[2] + oz;
+            mbar_wait(smem_u32(acc_full + acc), acc_phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            for (int c0 = 0; c0 < a.n_tile; c0 += 64) {
+                const int ncols = a.n_tile - c0 < 64 ? a.n_tile - c0 : 64;
+                uint8_t *slab_ptr = slab_base + slab * TC_A_BYTES;
+                // the TMA store that last read this slab must be done before we overwrite it
+                if (epi_leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                for (int h = 0; h < ncols; h += 32) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c0 + h, v);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const int ch = tc.n0 + c0 + h;
+#pragma unroll
+                    for (int j = 0; j < 32; j += 8) {
+                        float f[8];
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            const float sc = a.scale ? __ldg(a.scale + ch + j + e) : 1.f;
+                            const float sh = a.shift ? __ldg(a.shift + ch + j + e) : 0.f;
+                            f[e] = fmaf(__uint_as_float(v[j + e]), sc, sh);
+                        }
+                        float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                        if (a.res && row_ok) {
+                            const uint4 u = __ldg(reinterpret_cast<const uint4 *>(a.res + ovox * a.c_out + ch + j));
+                            const __nv_bfloat162 *p2 = reinterpret_cast<const __nv_bfloat162 *>(&u);
+#pragma unroll
+                            for (int e = 0; e < 4; ++e) {
+                                const float2 fr = __bfloat1622float2(p2[e]);
+                                r[2 * e] = fr.x, r[2 * e + 1] = fr.y;
+                            }
+                        }
+#pragma unroll
+                        for (int e = 0; e < 8; ++e) {
+                            if (a.res && !a.residual_after_act) f[e] += r[e];
+                            if (a.relu) f[e] = fmaxf(f[e], 0.f);
+                            if (a.res && a.residual_after_act) f[e] += r[e];
+                            f[e] *= a.post_scale;
+                        }
+                        uint4 o;
+                        __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
+                        __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
+                        o.x = *reinterpret_cast<uint32_t *>(&b0), o.y = *reinterpret_cast<uint32_t *>(&b1);
+                        o.z = *reinterpret_cast<uint32_t *>(&b2), o.w = *reinterpret_cast<uint32_t *>(&b3);
+                        const int chunk = (h + j) >> 3;  // 16-byte chunk inside the 128-byte row
+                        *reinterpret_cast<uint4 *>(slab_ptr + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+                    }
+                }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // st.shared -> visible to TMA
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (epi_leader) {
+                    tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.z0, tc.y0, tc.x0, tc.b);
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                slab ^= 1;
+            }
+            // accumulator fully read: hand it back to the MMA warp
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(acc_empty + acc));
+            if (++acc == 2) acc = 0, acc_phase ^= 1;
+        }
+        if (epi_leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// ------------------------------- host side --------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    if (fn == nullptr) {
+        void *p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    }
+    return fn;
+}
+
+static int encode_map(CUtensorMap *map, int rank, void *base, const cuuint64_t *dims,
+                      const cuuint64_t *strides_bytes, const cuuint32_t *box, const cuuint32_t *estrides,
+                      const char *what) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (fn == nullptr) return fail(IVX_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, base, dims, strides_bytes, box,
+                    estrides, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(IVX_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed with %d", what, (int)r);
+    return IVX_OK;
+}
+
+// box of output voxels with bx*by*bz <= 128 that wastes the fewest accumulator rows
+static void pick_box(const int32_t out[3], const int32_t stride[3], int box[3], int tiles[3]) {
+    double best = -1.0;
+    for (int bz = 1; bz <= out[2] && bz <= 128; ++bz) {
+        if (bz * stride[2] > 256) break;
+        for (int by = 1; by <= out[1] && bz * by <= 128; ++by) {
+            if (by * stride[1] > 256) break;
+            int bx = 128 / (bz * by);
+            if (bx > out[0]) bx = out[0];
+            if (bx * stride[0] > 256) bx = 256 / stride[0];
+            const long long t0 = (out[0] + bx - 1) / bx, t1 = (out[1] + by - 1) / by, t2 = (out[2] + bz - 1) / bz;
+            const double eff = (double)out[0] * out[1] * out[2] / (double)(t0 * t1 * t2 * 128);
+            // prefer long z runs on ties: they are contiguous in memory
+            if (eff > best + 1e-9) {
+                best = eff;
+                box[0] = bx, box[1] = by, box[2] = bz;
+                tiles[0] = (int)t0, tiles[1] = (int)t1, tiles[2] = (int)t2;
+            }
+        }
+    }
+}
+
+}  // namespace ivx
+
+using namespace ivx;
+
+extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *x, const void *weight_bf16,
+                                        const float *scale, const float *shift, const void *residual,
+                                        void *y, void *stream) {
+    IVX_REQUIRE(p && x && weight_bf16 && y, "NULL argument");
+    if (p->transposed || p->in_dtype != IVX_BF16 || p->out_dtype != IVX_BF16)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in/out, not transposed");
+    if (p->c_in % TC_KCHUNK != 0 || p->c_out % 64 != 0)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: c_in and c_out must be multiples of 64");
+    for (int d = 0; d < 3; ++d) {
+        const int expect = (p->in_dims[d] + 2 * p->pad[d] - p->kernel[d]) / p->stride[d] + 1;
+        IVX_REQUIRE(p->kernel[d] >= 1 && p->stride[d] >= 1 && p->stride[d] <= 8 && p->pad[d] >= 0 &&
+                        expect == p->out_dims[d] && p->out_dims[d] > 0,
+                    "bad geometry on axis %d", d);
+    }
+    IVX_REQUIRE(p->batch > 0, "batch must be positive");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+                 reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+
+    TcArgs a;
+    a.c_in = p->c_in, a.c_out = p->c_out;
+    a.n_tile = p->c_out % 256 == 0 ? 256 : (p->c_out % 128 == 0 && p->c_out > 128 ? 128 : (p->c_out <= 256 ? p->c_out : 64));
+    a.n_splits = p->c_out / a.n_tile;
+    for (int d = 0; d < 3; ++d) {
+        a.taps[d] = p->kernel[d], a.stride[d] = p->stride[d], a.pad[d] = p->pad[d];
+        a.out_dims[d] = p->out_dims[d];
+    }
+    a.batch = p->batch;
+    pick_box(p->out_dims, p->stride, a.box, a.tiles);
+    a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
+    a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
+    a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
+
+    const int stage_bytes = TC_A_BYTES + a.n_tile * 128;
+    const int fixed = 2 * TC_A_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;
+    a.stages = (227 * 1024 - fixed) / stage_bytes;
+    if (a.stages > 8) a.stages = 8;
+    IVX_REQUIRE(a.stages >= 2, "not enough shared memory for a 2-stage pipeline");
+    const size_t smem = (size_t)a.stages * stage_bytes + fixed;
+
+    alignas(64) CUtensorMap map_x, map_w, map_y;
+    {
+        const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[2], (cuuint64_t)p->in_dims[1],
+                                    (cuuint64_t)p->in_dims[0], (cuuint64_t)p->batch};
+        cuuint64_t st[4];
+        st[0] = (cuuint64_t)p->c_in * 2;
+        st[1] = st[0] * p->in_dims[2];
+        st[2] = st[1] * p->in_dims[1];
+        st[3] = st[2] * p->in_dims[0];
+        const cuuint32_t box[5] = {TC_KCHUNK, (cuuint32_t)(a.box[2] * p->stride[2]),
+                                   (cuuint32_t)(a.box[1] * p->stride[1]), (cuuint32_t)(a.box[0] * p->stride[0]), 1};
+        const cuuint32_t es[5] = {1, (cuuint32_t)p->stride[2], (cuuint32_t)p->stride[1], (cuuint32_t)p->stride[0], 1};
+        int rc = encode_map(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations");
+        if (rc != IVX_OK) return rc;
+    }
+    {
+        const int taps = p->kernel[0] * p->kernel[1] * p->kernel[2];
+        const cuuint64_t dims[2] = {(cuuint64_t)taps * p->c_in, (cuuint64_t)p->c_out};
+        const cuuint64_t st[1] = {(cuuint64_t)taps * p->c_in * 2};
+        const cuuint32_t box[2] = {TC_KCHUNK, (cuuint32_t)a.n_tile};
+        const cuuint32_t es[2] = {1, 1};
+        int rc = encode_map(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights");
+        if (rc != IVX_OK) return rc;
+    }
+    {
+        const cuuint64_t dims[5] = {(cuuint64_t)p->c_out, (cuuint64_t)p->out_dims[2], (cuuint64_t)p->out_dims[1],
+                                    (cuuint64_t)p->out_dims[0], (cuuint64_t)p->batch};
+        cuuint64_t st[4];
+        st[0] = (cuuint64_t)p->c_out * 2;
+        st[1] = st[0] * p->out_dims[2];
+        st[2] = st[1] * p->out_dims[1];
+        st[3] = st[2] * p->out_dims[0];
+        const cuuint32_t box[5] = {64, (cuuint32_t)a.box[2], (cuuint32_t)a.box[1], (cuuint32_t)a.box[0], 1};
+        const cuuint32_t es[5] = {1, 1, 1, 1, 1};
+        int rc = encode_map(&map_y, 5, y, dims, st, box, es, "output");
+        if (rc != IVX_OK) return rc;
+    }
+
+    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem),
+                        "cudaFuncSetAttribute");
+    if (rc != IVX_OK) return rc;
+    const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
+    conv3d_tc_kernel<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(map_x, map_w, map_y, a);
+    IVX_CHECK_LAUNCH("conv3d_tc launch");
+    return IVX_OK;
+}

@@ -1,0 +1,98 @@
+"""The tcgen05 Conv3d kernel against torch fp32 convolution of the same
+bf16-rounded operands (TF32 off).  Tolerance: the output is rounded to bf16
+(2^-9 relative), so |err| <= 1e-2 * max|ref| as the stated bf16 bar."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from imvoxelnet_b200 import conv
+from tests.util import assert_volume_close
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+CASES = [
+    # cin, cout, dims(X,Y,Z), kernel, stride, pad, batch
+    (64, 64, (6, 10, 12), 3, 1, 1, 1),
+    (64, 128, (9, 11, 12), 3, (1, 1, 2), 1, 2),
+    (128, 256, (7, 9, 6), 3, (1, 1, 2), 1, 1),
+    (256, 256, (6, 7, 3), 3, 1, 0, 1),
+    (64, 128, (12, 10, 12), 3, 2, 1, 1),
+    (256, 256, (8, 8, 3), 3, 1, (1, 1, 0), 1),
+    (256, 512, (8, 8, 4), 3, 2, 1, 2),
+    (512, 512, (5, 5, 4), 3, 1, 1, 1),
+    (256, 128, (10, 10, 16), 3, 1, 1, 1),
+    (256, 512, (8, 8, 4), 1, 2, 0, 1),
+    (128, 64, (8, 8, 8), 1, 1, 0, 1),
+]
+
+
+def _reference(x, layer, bn, relu, residual, after, post):
+    w = layer.weight.to(torch.bfloat16).float()
+    y = F.conv3d(x.float(), w, layer.bias, layer.stride, layer.padding)
+    if bn is not None:
+        y = F.batch_norm(y, bn.running_mean, bn.running_var, bn.weight, bn.bias, False, 0.0, bn.eps)
+    if residual is not None and not after:
+        y = y + residual.float()
+    if relu:
+        y = F.relu(y)
+    if residual is not None and after:
+        y = y + residual.float()
+    return y * post
+
+
+@pytest.fixture(autouse=True)
+def _no_tf32():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
+
+
+@pytest.mark.parametrize("case", CASES, ids=[str(c) for c in CASES])
+@pytest.mark.parametrize("variant", ["plain", "bn_relu_res", "res_after_half"])
+def test_tensor_core_conv(case, variant):
+    cin, cout, dims, k, stride, pad, batch = case
+    torch.manual_seed(hash((case, variant)) % 1000)
+    layer = nn.Conv3d(cin, cout, k, stride, pad, bias=(variant != "plain")).to(DEV)
+    bn = None
+    if variant != "plain":
+        bn = nn.BatchNorm3d(cout).to(DEV).eval()
+        with torch.no_grad():
+            bn.running_mean.normal_(0, .1), bn.running_var.uniform_(.5, 1.5)
+            bn.weight.uniform_(.5, 1.5), bn.bias.normal_(0, .1)
+    relu = variant != "plain"
+    fused = conv.FusedConv(layer, bn, relu=relu)
+    x = torch.randn((batch, cin) + dims, device=DEV).to(torch.bfloat16)
+    xn = conv.to_ndhwc(x)
+    od = fused.out_dims(dims)
+    residual = None
+    if variant != "plain":
+        residual = torch.randn((batch, cout) + od, device=DEV).to(torch.bfloat16)
+    after, post = (variant == "res_after_half"), (0.5 if variant == "res_after_half" else 1.0)
+    assert fused.tc_eligible(xn, torch.bfloat16)
+    with torch.no_grad():
+        got = fused(xn, residual=conv.to_ndhwc(residual) if residual is not None else None,
+                    residual_after_act=after, post_scale=post)
+        want = _reference(x, layer, bn, relu, residual, after, post)
+    got = conv.from_ndhwc(got).float()
+    assert got.shape == want.shape
+    assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-2, atol=1e-3)
+
+
+def test_cuda_core_bf16_path_agrees_with_tensor_cores():
+    torch.manual_seed(0)
+    layer = nn.Conv3d(64, 64, 3, 1, 1, bias=False).to(DEV)
+    fused = conv.FusedConv(layer, None, relu=True)
+    x = conv.to_ndhwc(torch.randn(1, 64, 8, 8, 8, device=DEV).to(torch.bfloat16))
+    with torch.no_grad():
+        a = fused(x)
+        conv.USE_TENSOR_CORES = False
+        try:
+            b = fused(x)
+        finally:
+            conv.USE_TENSOR_CORES = True
+    assert_volume_close(a.float().cpu().numpy(), b.float().cpu().numpy(), rel=1e-2, atol=1e-3)
