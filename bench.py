@@ -4,8 +4,9 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME]
     python bench.py --impl reference ...        # the reference's CPU path (port)
 
-One "step" = one pass of the hot path over one batch of synthetic scenes of
-the named configuration.  Default workload: ``imvoxelnet_kitti`` -- 1280x384
+One "step" = one pass of the hot path -- fused back-projection + view mean,
+then the configuration's 3D neck -- over one batch of synthetic scenes of the
+named configuration.  Default workload: ``imvoxelnet_kitti`` -- 1280x384
 monocular, 216x248x12 voxels, 64 channels, batch 8 (BASELINE.json configs[1]).
 For N > 1 every rank processes its own batch of scenes (plain data-parallel,
 no collective on the data path: "scaling": "weak"); ``--workload
@@ -41,7 +42,7 @@ WORKLOADS = {
     "nuscenes": ("nuscenes", 8),
     "total_sunrgbd": ("total_sunrgbd", 32),
 }
-METRIC = "backproject_voxel_views_per_s"
+METRIC = "voxel_views_per_s"   # through the whole hot path: back-projection + 3D neck
 UNIT = "voxel-views/s"
 
 
@@ -118,22 +119,55 @@ def config_of(sc, batch, world, extra=None):
     return cfg
 
 
+NECKS = {
+    # workload -> (neck class, constructor kwargs, dense GFLOP per scene: SURVEY.md appendix A)
+    "kitti": ("KittiImVoxelNeck", dict(in_channels=64, out_channels=256), 2603.37),
+    "scannet_fast": ("FastIndoorImVoxelNeck", dict(in_channels=256, n_blocks=[1, 1, 1], out_channels=128), 489.79),
+    "sunrgbd_fast": ("FastIndoorImVoxelNeck", dict(in_channels=256, n_blocks=[1, 1, 1], out_channels=128), 489.79),
+    "total_sunrgbd": ("ImVoxelNeck", dict(channels=[64, 128, 256, 512], out_channels=64,
+                                          down_layers=[1, 2, 3, 4], up_layers=[3, 2, 1], conditional=False), 631.66),
+    "nuscenes": None,   # BASELINE's 200x200x4 grid: every reference neck rejects Z=4
+}
+
+
+def randomize_norms(module, seed=0):
+    """Random BN affine / running statistics and non-zero bn2 weights, so the
+    random-init neck is not degenerate (hard parts)."""
+    g = torch.Generator().manual_seed(seed)
+    for m in module.modules():
+        if isinstance(m, torch.nn.BatchNorm3d):
+            with torch.no_grad():
+                m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+                m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.weight.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+                m.bias.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    return module
+
+
 # --------------------------------------------------------------------------
 # the reference arm: the reference's CPU path (torch port), all host threads
 # --------------------------------------------------------------------------
-def cpu_reference_time(sc, P, origin, repeats, warmup, seed=0):
-    """Seconds per scene of the reference's torch-CPU path (best of repeats)."""
-    from oracle import torch_port
+def cpu_reference_time(sc, P, origin, workload, repeats, warmup, with_neck, seed=0):
+    """Seconds per scene of the reference's torch-CPU path: backproject + view
+    mean (oracle/torch_port.py) and, if asked, the neck (oracle/torch_necks.py)."""
+    from oracle import torch_necks, torch_port
     torch.set_num_threads(os.cpu_count() or 1)
     full = scenes.random_features(sc, seed=seed, channels_last=False)
     h, w = sc.feat_hw
     feats = full[:, :, :h, :w]
     pts = pj.get_points(sc.n_voxels, sc.voxel_size, origin)
+    neck = None
+    if with_neck and NECKS[workload] is not None:
+        name, kw, _ = NECKS[workload]
+        torch.manual_seed(0)
+        neck = randomize_norms(torch_necks.NECKS[name](**kw).eval())
     times = []
     with torch.no_grad():
         for i in range(warmup + repeats):
             t0 = time.perf_counter()
-            torch_port.scene_volume(feats, pts, P)
+            vol, _ = torch_port.scene_volume(feats, pts, P)
+            if neck is not None:
+                neck(vol[None])
             dt = time.perf_counter() - t0
             if i >= warmup:
                 times.append(dt)
@@ -145,21 +179,26 @@ def run_reference(args):
     if rank != 0:
         return
     sc, batch, P, origin = scene_setup(args.workload)
+    with_neck = not args.no_neck and NECKS[args.workload] is not None
     # a step = ONE scene of the batch (bounded sample of the workload)
-    times = cpu_reference_time(sc, P, origin, repeats=args.steps, warmup=max(1, min(args.warmup, 2)))
+    times = cpu_reference_time(sc, P, origin, args.workload, repeats=args.steps,
+                               warmup=1 if with_neck else max(1, min(args.warmup, 2)), with_neck=with_neck)
     t = sum(times) / len(times)
     value = sc.voxel_views / t
     cores = os.cpu_count() or 1
+    stages = ["backproject+view-mean"] + (["3d-neck"] if with_neck else [])
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
-        "config": config_of(sc, batch, 1, {"note": "one scene per step (bounded sample of the batch)"}),
+        "config": config_of(sc, batch, 1, {"stages": stages,
+                                           "note": "one scene per step (bounded sample of the batch)"}),
+        "scenes_per_s": 1.0 / t,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{args.steps} x 1 scene of {sc.name}, torch {torch.__version__} "
-                                   f"CPU ops of the reference's backproject + view mean "
-                                   f"(oracle/torch_port.py), {cores} threads"},
+                         "sample": f"{args.steps} x 1 scene of {sc.name}: torch {torch.__version__} CPU "
+                                   f"ops of the reference's {' + '.join(stages)} (oracle/torch_port.py, "
+                                   f"oracle/torch_necks.py), {cores} threads"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -183,9 +222,33 @@ def algorithmic_bytes(sc, P, origin, device):
     return U * C * 4 + N * C * 4 + N + V * 48, U, n_valid
 
 
+def timed_graph(fn, steps, barrier, repeats=5):
+    """Capture ``steps`` calls of fn(i) in a CUDA graph; median ms of ``repeats``
+    timed replays (each exactly ``steps`` steps, synchronised on both sides)."""
+    graph = torch.cuda.CUDAGraph()
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            for i in range(steps):
+                fn(i)
+    torch.cuda.current_stream().wait_stream(side)
+    graph.replay()      # untimed: the first replay uploads the graph
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    totals = []
+    for _ in range(repeats):
+        barrier()
+        ev0.record()
+        graph.replay()
+        ev1.record()
+        barrier()
+        totals.append(ev0.elapsed_time(ev1))
+    return statistics.median(totals), graph
+
+
 def run_ours(args):
     import torch.distributed as dist
-    from imvoxelnet_b200 import _lib, ops, sharding
+    from imvoxelnet_b200 import _lib, conv, necks, ops, sharding
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -203,15 +266,19 @@ def run_ours(args):
     h, w = sc.feat_hw
     N, C, V = sc.n_total_voxels, sc.channels, sc.n_views
     b_algo, U, n_valid = algorithmic_bytes(sc, P, origin, dev)
-
-    if view_sharded:
-        my_views = list(range(rank, V, world))
-    else:
-        my_views = list(range(V))
+    my_views = list(range(rank, V, world)) if view_sharded else list(range(V))
     Vr = len(my_views)
 
+    neck = None
+    if not args.no_neck and NECKS[args.workload] is not None:
+        name, kw, neck_gflop = NECKS[args.workload]
+        torch.manual_seed(0)
+        neck = randomize_norms(getattr(necks, name)(**kw).eval()).to(dev)
+        neck.precision = args.neck_precision
+    vol_dtype = torch.bfloat16 if (neck is not None and args.neck_precision == "bf16") else torch.float32
+
     # rotating device input sets (> L2 in total, so no step finds its map in L2
-    # from the previous one; the 1.3 GB of output per step evicts it anyway)
+    # from the previous one; the output written per step evicts it anyway)
     n_sets = 3
     host = scenes.random_features(sc, seed=rank, batch=batch, channels_last=True)
     if view_sharded:
@@ -226,166 +293,193 @@ def run_ours(args):
     hws = [(h, w)] * batch
     origins = [origin] * batch
 
-    def step(i):
+    def backproject(feats, proj, out_dtype):
         if view_sharded:
-            return sharding.backproject_scenes_view_sharded(
-                dev_sets[i % n_sets], hws, P_dev, sc.n_voxels, sc.voxel_size, origins)
-        return ops.backproject_scenes(dev_sets[i % n_sets], hws, P_dev, sc.n_voxels, sc.voxel_size,
-                                      origins)
+            return sharding.backproject_scenes_view_sharded(feats, hws, proj, sc.n_voxels, sc.voxel_size,
+                                                            origins, out_dtype=out_dtype)
+        return ops.backproject_scenes(feats, hws, proj, sc.n_voxels, sc.voxel_size, origins,
+                                      out_dtype=out_dtype)
+
+    def bp_step(i):                      # stage 1 alone, fp32 volume (the parity dtype)
+        return backproject(dev_sets[i % n_sets], P_dev, torch.float32)
+
+    def bp_step_as_in_step(i):           # stage 1 alone, volume dtype of the full step
+        return backproject(dev_sets[i % n_sets], P_dev, vol_dtype)
+
+    def step(i):                         # the whole hot path
+        vol, valid, _ = backproject(dev_sets[i % n_sets], P_dev, vol_dtype)
+        return (neck(vol) if neck is not None else [vol]), valid
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(args.warmup):
-        step(i)
-    barrier()
+    def count_launches():
+        return ops.launch_count() + conv.launch_count()
 
-    # ---- device-resident timing ----
-    # The K steps are captured once into a CUDA graph and replayed, so that the
-    # timed region holds K back-to-back passes with no host launch gaps (a step
-    # of the small configurations is shorter than one Python call).  With a
-    # collective in the step (view-sharded mode) the steps are issued eagerly.
-    sampler = ClockSampler(local)
-    use_graph = not view_sharded
-    launches0 = ops.launch_count()
-    if use_graph:
-        graph = torch.cuda.CUDAGraph()
-        side = torch.cuda.Stream()
-        side.wait_stream(torch.cuda.current_stream())
-        with torch.cuda.stream(side):
-            with torch.cuda.graph(graph, stream=side):
-                for i in range(args.steps):
-                    step(i)
-        torch.cuda.current_stream().wait_stream(side)
-        launches = ops.launch_count() - launches0   # kernels captured = launched per replay
-        graph.replay()                              # untimed: first replay uploads the graph
+    with torch.no_grad():
+        for i in range(args.warmup):
+            step(i)
         barrier()
-    if rank == 0:
-        sampler.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    repeats = 5 if use_graph else 1
-    totals = []
-    for _ in range(repeats):
-        barrier()
-        ev0.record()
+
+        # ---- device-resident timing ----
+        # K steps are captured once into a CUDA graph and replayed: the timed region
+        # holds K back-to-back passes with no host launch gaps (a back-projection of
+        # the small configurations is shorter than one Python call).  With a
+        # collective in the step (view-sharded mode) the steps are issued eagerly.
+        sampler = ClockSampler(local)
+        use_graph = not view_sharded
+        launches0 = count_launches()
         if use_graph:
-            graph.replay()
+            bp_ms_total, _g1 = timed_graph(bp_step, args.steps, barrier)
+            bp_in_step_total = bp_ms_total
+            if vol_dtype != torch.float32:
+                bp_in_step_total, _g3 = timed_graph(bp_step_as_in_step, args.steps, barrier)
+            launches0 = count_launches()
+            if rank == 0:
+                sampler.start()
+            total_ms, _g2 = timed_graph(step, args.steps, barrier)
+            launches = count_launches() - launches0      # kernels captured = launched per replay
         else:
+            if rank == 0:
+                sampler.start()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            ev0.record()
+            for i in range(args.steps):
+                bp_step(i)
+            ev1.record()
+            barrier()
+            bp_ms_total = bp_in_step_total = ev0.elapsed_time(ev1)
+            launches0 = count_launches()
+            barrier()
+            ev0.record()
             for i in range(args.steps):
                 step(i)
+            ev1.record()
+            barrier()
+            total_ms = ev0.elapsed_time(ev1)
+            launches = count_launches() - launches0
+        t = torch.tensor([total_ms, bp_ms_total, bp_in_step_total], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        total_ms, bp_ms_total, bp_in_step_total = (float(v) for v in t.tolist())
+        ms_per_step = total_ms / args.steps
+        bp_ms = bp_ms_total / args.steps
+        bp_in_step_ms = bp_in_step_total / args.steps
+        clocks = sampler.stop() if rank == 0 else None
+        # eager issue of the same K steps, for the record (host-launch bound when short)
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        for i in range(args.steps):
+            step(i)
         ev1.record()
         barrier()
-        totals.append(ev0.elapsed_time(ev1))
-    if not use_graph:
-        launches = ops.launch_count() - launches0
-    total_ms = statistics.median(totals)            # of 5 timed runs of exactly K steps each
-    t = torch.tensor([total_ms], device=dev, dtype=torch.float64)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms = float(t.item())
-    ms_per_step = total_ms / args.steps
-    clocks = sampler.stop() if rank == 0 else None
-    # eager issue of the same K steps, for the record (host-launch bound when short)
-    barrier()
-    ev0.record()
-    for i in range(args.steps):
-        step(i)
-    ev1.record()
-    barrier()
-    eager_ms_per_step = ev0.elapsed_time(ev1) / args.steps
+        eager_ms_per_step = ev0.elapsed_time(ev1) / args.steps
 
     scenes_global = batch * (1 if view_sharded else world)
     units_per_step = scenes_global * V * N
     value = units_per_step / (ms_per_step * 1e-3)
-
-    # dominant kernel: the fused back-projection; its launch duration is the
-    # step (one launch per step) unless the step also holds the collective
-    kern_ms = ms_per_step if not view_sharded else None
     peaks, peak_kind = load_peaks()
-    if kern_ms is not None:
-        achieved = b_algo * batch / (kern_ms * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
-                    "frac": achieved / peaks["hbm_gbs"], "traffic": _ncu_traffic(sc.name),
-                    "kernel": "bp_vec_kernel", "peak_kind": peak_kind,
-                    "algorithmic_bytes_per_launch": b_algo * batch,
-                    "kernel_ms": kern_ms, "distinct_pixels_per_scene": U,
-                    "valid_voxel_views_per_scene": n_valid}
-    else:
-        roofline = None
+
+    roofline_bp = None
+    if not view_sharded:
+        achieved = b_algo * batch / (bp_ms * 1e-3) / 1e9
+        roofline_bp = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                       "frac": achieved / peaks["hbm_gbs"], "traffic": _ncu_traffic(sc.name),
+                       "kernel": "bp_vec_kernel", "peak_kind": peak_kind,
+                       "algorithmic_bytes_per_launch": b_algo * batch, "kernel_ms": bp_ms,
+                       "distinct_pixels_per_scene": U, "valid_voxel_views_per_scene": n_valid}
+    stages = {"backproject": {"ms": bp_ms, "voxel_views_per_s": units_per_step / (bp_ms * 1e-3),
+                              "volume_dtype": "f32", "ms_inside_step": bp_in_step_ms,
+                              "volume_dtype_inside_step": str(vol_dtype).replace("torch.", "")}}
+    roofline = roofline_bp
+    if neck is not None:
+        neck_ms = max(ms_per_step - bp_in_step_ms, 1e-6)   # full step minus its back-projection
+        tflops = neck_gflop * batch / neck_ms                      # GFLOP / ms == TFLOP/s
+        peak = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+        stages["neck"] = {"ms": neck_ms, "tflops": tflops, "precision": args.neck_precision,
+                          "gflop_per_scene": neck_gflop, "module": type(neck).__name__}
+        if args.neck_precision == "bf16":
+            # dominant kernel of the step: conv3d_tc_kernel (tcgen05 implicit GEMM), timed inside a long step
+            roofline = {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
+                        "frac": tflops / peak, "frac_of_burst_peak": tflops / peaks["bf16_tflops"],
+                        "traffic": None, "kernel": "conv3d_tc_kernel", "peak_kind": peak_kind + " (sustained)",
+                        "algorithmic_flops_per_step": neck_gflop * batch * 1e9,
+                        "launches_per_step": launches // max(args.steps, 1) - 1}
 
     # ---- end to end: host buffers in, host buffers out, every step ----
-    out0 = step(0)
-    vol_host = _pinned_like(out0[0])
-    val_host = _pinned_like(out0[1])
-    h2d = host_pinned.numel() * 4 + Pb.numel() * 4
-    d2h = vol_host.numel() * vol_host.element_size() + val_host.numel()
-    P_pinned = Pb.pin_memory()
-    e2e_steps = max(3, min(args.steps, 10))
+    with torch.no_grad():
+        out0 = step(0)
+        res_host = [_pinned_like(o) for o in out0[0]]
+        val_host = _pinned_like(out0[1])
+        h2d = host_pinned.numel() * 4 + Pb.numel() * 4
+        d2h = sum(r.numel() * r.element_size() for r in res_host) + val_host.numel()
+        P_pinned = Pb.pin_memory()
+        e2e_steps = max(3, min(args.steps, 10))
 
-    def e2e_step():
-        feats = host_pinned.to(dev, non_blocking=True)
-        pd = P_pinned.to(dev, non_blocking=True)
-        if view_sharded:
-            out = sharding.backproject_scenes_view_sharded(feats, hws, pd, sc.n_voxels,
-                                                           sc.voxel_size, origins)
-        else:
-            out = ops.backproject_scenes(feats, hws, pd, sc.n_voxels, sc.voxel_size, origins)
-        vol_host.copy_(out[0], non_blocking=True)
-        val_host.copy_(out[1], non_blocking=True)
+        def e2e_step():
+            feats = host_pinned.to(dev, non_blocking=True)
+            pd = P_pinned.to(dev, non_blocking=True)
+            vol, valid, _ = backproject(feats, pd, vol_dtype)
+            outs = neck(vol) if neck is not None else [vol]
+            for r, o in zip(res_host, outs):
+                r.copy_(o, non_blocking=True)
+            val_host.copy_(valid, non_blocking=True)
 
-    e2e_step()
-    barrier()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for _ in range(e2e_steps):
         e2e_step()
-    e1.record()
-    barrier()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(e2e_steps):
+            e2e_step()
+        e1.record()
+        barrier()
     t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     e2e_ms = float(t.item()) / e2e_steps
     e2e = {"value": units_per_step / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps,
-           "api": "imvoxelnet_b200.ops.backproject_scenes (ivx_backproject_scenes), pinned host "
-                  "features + projections in, fp32 volume + valid mask out"}
+           "scenes_per_s": scenes_global / (e2e_ms * 1e-3),
+           "api": "ops.backproject_scenes (ivx_backproject_scenes) + neck module forward "
+                  "(ivx_conv3d_ndhwc*); pinned host features + projections in, neck outputs + valid "
+                  "mask out to pinned host memory"}
 
     if rank == 0:
         cpu = None
         if world == 1:
-            times = cpu_reference_time(sc, P, origin, repeats=3, warmup=1)
+            times = cpu_reference_time(sc, P, origin, args.workload, repeats=2 if neck is not None else 3,
+                                       warmup=1, with_neck=neck is not None)
             tcpu = min(times)
             cores = os.cpu_count() or 1
             cpu = {"value": sc.voxel_views / tcpu, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"best of 3 x 1 scene of {sc.name} (torch-CPU port of the reference's "
-                             f"backproject + view mean, oracle/torch_port.py)",
-                   "ms_per_scene": tcpu * 1e3}
-            try:
-                from oracle import backproject as ob
-                full = scenes.random_features(sc, seed=0, channels_last=False).numpy()
-                pts = ob.get_points(sc.n_voxels, sc.voxel_size, origin)
-                t0 = time.perf_counter()
-                ob.backproject_mean(full[:, :, :h, :w], pts, P.numpy())
-                cpu["c_oracle_openmp_value"] = sc.voxel_views / (time.perf_counter() - t0)
-            except Exception as exc:  # the C oracle is optional for the bench
-                cpu["c_oracle_openmp_value"] = f"unavailable: {exc}"
+                   "sample": f"best of {len(times)} x 1 scene of {sc.name}: torch-CPU port of the "
+                             f"reference's backproject + view mean"
+                             f"{' + 3D neck' if neck is not None else ''} (oracle/torch_port.py, "
+                             f"oracle/torch_necks.py)",
+                   "ms_per_scene": tcpu * 1e3, "scenes_per_s": 1.0 / tcpu}
+        stage_names = ["backproject+view-mean"] + (["3d-neck"] if neck is not None else [])
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-            "scaling": "strong" if view_sharded else "weak", "vs_baseline": None, "dtype": "f32",
+            "scaling": "strong" if view_sharded else "weak", "vs_baseline": None,
+            "dtype": "f32 back-projection" + (f", {args.neck_precision} neck" if neck is not None else ""),
             "data": "synthetic",
             "config": config_of(sc, batch, world, {
+                "stages": stage_names,
                 "parallelism": (f"views sharded over {world} ranks + NCCL all-reduce" if view_sharded
                                 else f"scenes data-parallel x{world}, no collective"),
-                "l2": f"{n_sets} rotating input sets + {d2h / 1e6:.0f} MB written per step (> 126 MB L2)",
-                "layout": "features NHWC fp32, volume NDHWC fp32"}),
+                "l2": f"{n_sets} rotating input sets; activations written per step >> 126 MB L2",
+                "layout": "features NHWC fp32, volume and neck activations NDHWC"}),
             "scenes_per_s": scenes_global / (ms_per_step * 1e-3),
+            "stages": stages,
             "timing": {"mode": "cuda-graph replay of K steps, median of 5" if use_graph else "eager",
                        "eager_ms_per_step": eager_ms_per_step},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "clocks": clocks,
-            "gpu_launches": launches, "lib": _lib.version(),
+            "roofline": roofline, "roofline_backproject": roofline_bp, "cpu_baseline": cpu, "e2e": e2e,
+            "clocks": clocks, "gpu_launches": launches, "lib": _lib.version(),
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -422,6 +516,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti", choices=sorted(WORKLOADS))
+    ap.add_argument("--neck-precision", default="bf16", choices=["bf16", "fp32"],
+                    help="bf16: tcgen05 kernels (1e-2 of the reference); fp32: CUDA-core parity path (1e-5)")
+    ap.add_argument("--no-neck", action="store_true", help="time the back-projection stage only")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

@@ -83,3 +83,30 @@ def test_weights_are_repacked_after_a_state_dict_load():
         b = m(torch.from_numpy(g["x"]).to(DEV))[0]
     assert_volume_close(b.cpu().numpy(), g["out0"])
     assert not torch.equal(a, b)
+
+
+# bf16 mode: bf16 activations between layers, tcgen05 kernels for every layer with
+# channel counts that are multiples of 64.  Stated bar: 1e-2 of max|ref| per output
+# (north_star), with a small atol for outputs that are mostly zero after the ReLU.
+BF16_RTOL = 1e-2
+
+
+@pytest.mark.parametrize("name", sorted(BIGGER))
+def test_neck_bf16_mode(name):
+    kw, shape = BIGGER[name]
+    torch.manual_seed(13)
+    ref = torch_necks.NECKS[name](**kw).eval()
+    torch_necks.randomize_norms(ref, 6)
+    m = getattr(necks, name)(**kw).eval()
+    m.load_state_dict(ref.state_dict())
+    m.precision = "bf16"
+    ref.to(DEV), m.to(DEV)
+    x = torch.randn(shape, device=DEV)
+    with torch.no_grad():
+        want = ref(x)
+        got = m(x)
+    for a, b in zip(got, want):
+        assert a.dtype == torch.bfloat16 and a.shape == b.shape
+        err = (a.float() - b).abs().max().item() / b.abs().max().item()
+        print(name, tuple(b.shape), "bf16 max err / max|ref| = %.4f" % err)
+        assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)

@@ -5,7 +5,10 @@ for w in kitti scannet_fast sunrgbd_fast nuscenes total_sunrgbd; do
   python - <<PY
 import json
 d=json.load(open("gpurun_out/bench_$w.json"))
-r=d["roofline"]
-print("$w", "ms/step %.4f"%d["ms_per_step"], "eager %.4f"%d["timing"]["eager_ms_per_step"], "value %.3g"%d["value"], "GB/s %.0f frac %.3f"%(r["achieved"], r["frac"]), "e2e %.3g"%d["e2e"]["value"], "cpu %.3g"%d["cpu_baseline"]["value"], d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
+r=d["roofline_backproject"]; st=d["stages"]
+nk=st.get("neck")
+print("$w", "step %.3f ms"%d["ms_per_step"], "| bp %.4f ms %.0f GB/s frac %.3f"%(st["backproject"]["ms"], r["achieved"], r["frac"]),
+      "| neck " + ("%.2f ms %.0f TF/s frac %.3f"%(nk["ms"], nk["tflops"], d["roofline"]["frac"]) if nk else "-"),
+      "| scenes/s %.0f e2e %.0f cpu %.3g"%(d["scenes_per_s"], d["e2e"]["scenes_per_s"], d["cpu_baseline"]["scenes_per_s"]), d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
 PY
 done

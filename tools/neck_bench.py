@@ -1,0 +1,108 @@
+#!/usr/bin/env python
+"""Time the 3D necks layer by layer and as a whole (GPU box).
+
+    python tools/neck_bench.py [--neck KittiImVoxelNeck] [--batch 8] [--precision bf16]
+
+Prints per-layer ms / TFLOP/s of the fused conv kernels, the whole-neck time
+and the same neck in stock PyTorch (cuDNN) fp32 / TF32 / bf16 channels_last_3d
+as the same-box reference bar."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+from imvoxelnet_b200 import conv, necks  # noqa: E402
+
+CONFIGS = {
+    "KittiImVoxelNeck": (dict(in_channels=64, out_channels=256), (64, 216, 248, 12), 2603.37),
+    "NuScenesImVoxelNeck": (dict(in_channels=64, out_channels=256), (64, 312, 312, 12), 1571.76),
+    "FastIndoorImVoxelNeck": (dict(in_channels=256, n_blocks=[1, 1, 1], out_channels=128), (256, 40, 40, 16), 489.79),
+    "ImVoxelNeck": (dict(channels=[64, 128, 256, 512], out_channels=64, down_layers=[1, 2, 3, 4],
+                         up_layers=[3, 2, 1], conditional=False), (64, 80, 80, 32), 631.66),
+}
+
+
+def timed(fn, reps=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--neck", default="KittiImVoxelNeck")
+    ap.add_argument("--batch", type=int, default=8)
+    ap.add_argument("--precision", default="bf16")
+    ap.add_argument("--layers", action="store_true")
+    ap.add_argument("--torch-ref", action="store_true")
+    args = ap.parse_args()
+    kw, shape, gflop = CONFIGS[args.neck]
+    dev = "cuda:0"
+    torch.manual_seed(0)
+    m = getattr(necks, args.neck)(**kw).eval().to(dev)
+    m.precision = args.precision
+    x = torch.randn((args.batch,) + shape, device=dev).contiguous(memory_format=torch.channels_last_3d)
+    if args.precision == "bf16":
+        x = x.to(torch.bfloat16)
+    out = {"neck": args.neck, "batch": args.batch, "precision": args.precision}
+    if args.layers:
+        records = []
+        orig = conv.FusedConv.__call__
+
+        def wrapped(self, xx, **k):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            y = orig(self, xx, **k)
+            e1.record()
+            torch.cuda.synchronize()
+            ks = self.conv.kernel_size
+            taps = ks[0] * ks[1] * ks[2]
+            rows = y.numel() // y.shape[-1] if not self.transposed else xx.numel() // xx.shape[-1]
+            fl = 2.0 * rows * self.conv.in_channels * self.conv.out_channels * taps
+            records.append((tuple(xx.shape), tuple(y.shape), ks, self.conv.stride, e0.elapsed_time(e1), fl,
+                            self.tc_eligible(xx, y.dtype)))
+            return y
+
+        with torch.no_grad():
+            m(x)
+            conv.FusedConv.__call__ = wrapped
+            m(x)
+            conv.FusedConv.__call__ = orig
+        for r in records:
+            print("%-28s -> %-28s k%s s%s %8.3f ms %8.1f TFLOP/s %s" %
+                  (r[0], r[1], r[2][0], r[3], r[4], r[5] / r[4] / 1e9, "tc" if r[6] else "simt"))
+    with torch.no_grad():
+        ms = timed(lambda: m(x))
+    out["ms"] = ms
+    out["tflops"] = gflop * args.batch / ms
+    out["frac_of_bf16_burst_peak"] = out["tflops"] / 1616.4
+    if args.torch_ref:
+        sys.path.insert(0, ROOT)
+        from oracle import torch_necks
+        ref = torch_necks.NECKS[args.neck](**kw).eval().to(dev)
+        xr = x.float()
+        with torch.no_grad():
+            torch.backends.cudnn.allow_tf32 = False
+            out["torch_fp32_ms"] = timed(lambda: ref(xr), reps=2, warm=1)
+            torch.backends.cudnn.allow_tf32 = True
+            out["torch_tf32_ms"] = timed(lambda: ref(xr), reps=2, warm=1)
+            refb = ref.to(torch.bfloat16).to(memory_format=torch.channels_last_3d)
+            xb = xr.to(torch.bfloat16).contiguous(memory_format=torch.channels_last_3d)
+            out["torch_bf16_cl3d_ms"] = timed(lambda: refb(xb), reps=2, warm=1)
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()
