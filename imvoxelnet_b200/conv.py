@@ -88,16 +88,21 @@ class FusedConv:
         return self._packed[1:]
 
     def packed_tc(self, device):
-        """bf16 weights [Cout][taps][Cin] for the tensor-core kernel (+ fp32 scale/shift)."""
+        """bf16 weights for the tensor-core kernel (+ fp32 scale/shift)."""
         _, scale, shift = self.packed(device)
         if self._packed_tc is None:
             with torch.no_grad():
                 w = self.conv.weight.detach().to(device=device, dtype=torch.float32)
-                self._packed_tc = w.permute(0, 2, 3, 4, 1).contiguous().to(torch.bfloat16)
+                if self.transposed:   # [Cin, Cout, kx, ky, kz] -> [taps][Cout][Cin]
+                    self._packed_tc = w.permute(2, 3, 4, 1, 0).contiguous().to(torch.bfloat16)
+                else:                 # [Cout, Cin, kx, ky, kz] -> [Cout][taps][Cin]
+                    self._packed_tc = w.permute(0, 2, 3, 4, 1).contiguous().to(torch.bfloat16)
         return self._packed_tc, scale, shift
 
-    def tc_eligible(self, x, out_dtype):
-        return (not self.transposed and x.dtype == torch.bfloat16 and out_dtype == torch.bfloat16
+    def tc_eligible(self, x, out_dtype, residual=None):
+        if self.transposed and residual is not None:
+            return False
+        return (x.dtype == torch.bfloat16 and out_dtype == torch.bfloat16
                 and self.conv.in_channels % 64 == 0 and self.conv.out_channels % 64 == 0
                 and USE_TENSOR_CORES)
 
@@ -134,7 +139,7 @@ class FusedConv:
             assert residual.shape == y.shape and residual.dtype == y.dtype and residual.is_contiguous()
         res_ptr = residual.data_ptr() if residual is not None else None
         with torch.cuda.device(x.device):
-            if self.tc_eligible(x, out_dtype):
+            if self.tc_eligible(x, out_dtype, residual):
                 wt, scale, shift = self.packed_tc(x.device)
                 _lib.check(_lib.lib().ivx_conv3d_ndhwc_bf16_tc(
                     p, x.data_ptr(), wt.data_ptr(), scale.data_ptr() if scale is not None else None,

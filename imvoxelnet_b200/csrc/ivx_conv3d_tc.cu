@@ -47,6 +47,11 @@ struct TcArgs {
     float post_scale;
     const float *scale, *shift;
     const __nv_bfloat16 *res;
+    // transposed layers (ConvTranspose3d, kernel == stride): rows are INPUT voxels, the GEMM
+    // columns are (tap, c_out); every n-tile lies inside one tap and is stored with that
+    // tap's offset through an output map whose element strides are the layer stride
+    int transposed;
+    int up[3];                  // upsampling factor = kernel = stride of the transposed layer
 };
 
 // ------------------------------ PTX wrappers ------------------------------
@@ -283,6 +288,9 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         int slab = 0;
         for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
             const TileCoord tc = decode_tile(a, t);
+            const int tap_t = a.transposed ? tc.n0 / a.c_out : 0;   // which (kx,ky,kz) this n-tile is
+            const int ch0 = a.transposed ? tc.n0 - tap_t * a.c_out : tc.n0;
+            const int tkz = tap_t % a.up[2], tky = (tap_t / a.up[2]) % a.up[1], tkx = tap_t / (a.up[2] * a.up[1]);
             const int ox = tc.x0 + ix, oy = tc.y0 + iy, oz = tc.z0 + iz;
             const bool row_ok = row < box_rows && ox < a.out_dims[0] && oy < a.out_dims[1] && oz < a.out_dims[2];
             const long long ovox = (((long long)tc.b * a.out_dims[0] + ox) * a.out_dims[1] + oy) * a.out_dims[2] + oz;
@@ -298,7 +306,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     uint32_t v[32];
                     tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c0 + h, v);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    const int ch = tc.n0 + c0 + h;
+                    const int ch = ch0 + c0 + h;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
                         float f[8];
@@ -337,7 +345,11 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // st.shared -> visible to TMA
                 asm volatile("bar.sync 1, 128;" ::: "memory");
                 if (epi_leader) {
-                    tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.z0, tc.y0, tc.x0, tc.b);
+                    if (a.transposed)
+                        tma_store_5d(&map_y, smem_u32(slab_ptr), ch0 + c0, tc.z0 * a.up[2] + tkz,
+                                     tc.y0 * a.up[1] + tky, tc.x0 * a.up[0] + tkx, tc.b);
+                    else
+                        tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.z0, tc.y0, tc.x0, tc.b);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
                 slab ^= 1;
@@ -416,15 +428,21 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
                                         const float *scale, const float *shift, const void *residual,
                                         void *y, void *stream) {
     IVX_REQUIRE(p && x && weight_bf16 && y, "NULL argument");
-    if (p->transposed || p->in_dtype != IVX_BF16 || p->out_dtype != IVX_BF16)
-        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in/out, not transposed");
+    if (p->in_dtype != IVX_BF16 || p->out_dtype != IVX_BF16)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in and out only");
     if (p->c_in % TC_KCHUNK != 0 || p->c_out % 64 != 0)
         return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: c_in and c_out must be multiples of 64");
+    if (p->transposed && residual != nullptr)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: transposed layers take no residual");
     for (int d = 0; d < 3; ++d) {
-        const int expect = (p->in_dims[d] + 2 * p->pad[d] - p->kernel[d]) / p->stride[d] + 1;
+        const int expect = p->transposed ? p->in_dims[d] * p->stride[d]
+                                         : (p->in_dims[d] + 2 * p->pad[d] - p->kernel[d]) / p->stride[d] + 1;
         IVX_REQUIRE(p->kernel[d] >= 1 && p->stride[d] >= 1 && p->stride[d] <= 8 && p->pad[d] >= 0 &&
                         expect == p->out_dims[d] && p->out_dims[d] > 0,
                     "bad geometry on axis %d", d);
+        if (p->transposed)
+            IVX_REQUIRE(p->kernel[d] == p->stride[d] && p->pad[d] == 0,
+                        "transposed layers need kernel == stride and no padding (axis %d)", d);
     }
     IVX_REQUIRE(p->batch > 0, "batch must be positive");
     IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
@@ -433,14 +451,23 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
 
     TcArgs a;
     a.c_in = p->c_in, a.c_out = p->c_out;
-    a.n_tile = p->c_out % 256 == 0 ? 256 : (p->c_out % 128 == 0 && p->c_out > 128 ? 128 : (p->c_out <= 256 ? p->c_out : 64));
-    a.n_splits = p->c_out / a.n_tile;
+    a.transposed = p->transposed;
+    const int up_taps = p->transposed ? p->kernel[0] * p->kernel[1] * p->kernel[2] : 1;
+    const int n_total = p->c_out * up_taps;      // GEMM columns
+    a.n_tile = p->c_out % 256 == 0 ? 256 : (p->c_out % 128 == 0 ? 128 : 64);
+    a.n_splits = n_total / a.n_tile;
+    const int32_t ones[3] = {1, 1, 1};
+    const int32_t *row_dims = p->transposed ? p->in_dims : p->out_dims;   // what the tiles cover
+    const int32_t *ld_stride = p->transposed ? ones : p->stride;          // element strides of the loads
     for (int d = 0; d < 3; ++d) {
-        a.taps[d] = p->kernel[d], a.stride[d] = p->stride[d], a.pad[d] = p->pad[d];
-        a.out_dims[d] = p->out_dims[d];
+        a.taps[d] = p->transposed ? 1 : p->kernel[d];
+        a.stride[d] = ld_stride[d];
+        a.pad[d] = p->transposed ? 0 : p->pad[d];
+        a.out_dims[d] = row_dims[d];
+        a.up[d] = p->transposed ? p->stride[d] : 1;
     }
     a.batch = p->batch;
-    pick_box(p->out_dims, p->stride, a.box, a.tiles);
+    pick_box(row_dims, p->transposed ? p->stride : ld_stride, a.box, a.tiles);
     a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
     a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
@@ -461,15 +488,16 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         st[1] = st[0] * p->in_dims[2];
         st[2] = st[1] * p->in_dims[1];
         st[3] = st[2] * p->in_dims[0];
-        const cuuint32_t box[5] = {TC_KCHUNK, (cuuint32_t)(a.box[2] * p->stride[2]),
-                                   (cuuint32_t)(a.box[1] * p->stride[1]), (cuuint32_t)(a.box[0] * p->stride[0]), 1};
-        const cuuint32_t es[5] = {1, (cuuint32_t)p->stride[2], (cuuint32_t)p->stride[1], (cuuint32_t)p->stride[0], 1};
+        const cuuint32_t box[5] = {TC_KCHUNK, (cuuint32_t)(a.box[2] * ld_stride[2]),
+                                   (cuuint32_t)(a.box[1] * ld_stride[1]), (cuuint32_t)(a.box[0] * ld_stride[0]), 1};
+        const cuuint32_t es[5] = {1, (cuuint32_t)ld_stride[2], (cuuint32_t)ld_stride[1], (cuuint32_t)ld_stride[0], 1};
         int rc = encode_map(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations");
         if (rc != IVX_OK) return rc;
     }
     {
-        const int taps = p->kernel[0] * p->kernel[1] * p->kernel[2];
-        const cuuint64_t dims[2] = {(cuuint64_t)taps * p->c_in, (cuuint64_t)p->c_out};
+        // [c_out][taps * c_in] for convolutions, [taps * c_out][c_in] for transposed layers
+        const int taps = p->transposed ? 1 : p->kernel[0] * p->kernel[1] * p->kernel[2];
+        const cuuint64_t dims[2] = {(cuuint64_t)taps * p->c_in, (cuuint64_t)n_total};
         const cuuint64_t st[1] = {(cuuint64_t)taps * p->c_in * 2};
         const cuuint32_t box[2] = {TC_KCHUNK, (cuuint32_t)a.n_tile};
         const cuuint32_t es[2] = {1, 1};
@@ -484,8 +512,9 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         st[1] = st[0] * p->out_dims[2];
         st[2] = st[1] * p->out_dims[1];
         st[3] = st[2] * p->out_dims[0];
-        const cuuint32_t box[5] = {64, (cuuint32_t)a.box[2], (cuuint32_t)a.box[1], (cuuint32_t)a.box[0], 1};
-        const cuuint32_t es[5] = {1, 1, 1, 1, 1};
+        const cuuint32_t box[5] = {64, (cuuint32_t)(a.box[2] * a.up[2]), (cuuint32_t)(a.box[1] * a.up[1]),
+                                   (cuuint32_t)(a.box[0] * a.up[0]), 1};
+        const cuuint32_t es[5] = {1, (cuuint32_t)a.up[2], (cuuint32_t)a.up[1], (cuuint32_t)a.up[0], 1};
         int rc = encode_map(&map_y, 5, y, dims, st, box, es, "output");
         if (rc != IVX_OK) return rc;
     }

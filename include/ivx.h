@@ -280,9 +280,11 @@ IVX_API int ivx_conv3d_ndhwc(const ivx_conv3d_params *params, const void *x, con
  * implicit GEMM with tcgen05.mma (bf16 operands, fp32 accumulation in TMEM),
  * activations and weights staged by TMA (the zero padding is the TMA's
  * out-of-bounds fill), fused epilogue as above, bf16 in and out (1e-2 mode).
- * weight: bf16, [c_out][kX*kY*kZ][c_in].  Returns IVX_ERR_UNSUPPORTED for
- * shapes it does not take (transposed layers, c_in or c_out not a multiple of
- * 64, non-bf16 tensors): callers then use ivx_conv3d_ndhwc.
+ * weight: bf16, [c_out][kX*kY*kZ][c_in]; for transposed layers (kernel ==
+ * stride, stored through a strided TMA map) [kX*kY*kZ][c_out][c_in] and no
+ * residual.  Returns IVX_ERR_UNSUPPORTED for shapes it does not take (c_in or
+ * c_out not a multiple of 64, non-bf16 tensors): callers then use
+ * ivx_conv3d_ndhwc.
  */
 IVX_API int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *params, const void *x,
                                      const void *weight_bf16, const float *scale, const float *shift,

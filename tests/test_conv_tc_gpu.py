@@ -96,3 +96,26 @@ def test_cuda_core_bf16_path_agrees_with_tensor_cores():
         finally:
             conv.USE_TENSOR_CORES = True
     assert_volume_close(a.float().cpu().numpy(), b.float().cpu().numpy(), rel=1e-2, atol=1e-3)
+
+
+@pytest.mark.parametrize("cin,cout,dims,batch", [(128, 64, (5, 6, 4), 2), (1024, 512, (10, 10, 4), 1),
+                                                  (512, 256, (20, 20, 8), 1)])
+def test_tensor_core_transposed_conv(cin, cout, dims, batch):
+    """ConvTranspose3d(k=2, s=2) + BN + ReLU of the FastIndoor up blocks (:57-59)."""
+    torch.manual_seed(cin)
+    layer = nn.ConvTranspose3d(cin, cout, 2, 2, bias=False).to(DEV)
+    bn = nn.BatchNorm3d(cout).to(DEV).eval()
+    with torch.no_grad():
+        bn.running_mean.normal_(0, .1), bn.running_var.uniform_(.5, 1.5)
+        bn.weight.uniform_(.5, 1.5), bn.bias.normal_(0, .1)
+    fused = conv.FusedConv(layer, bn, relu=True)
+    x = torch.randn((batch, cin) + dims, device=DEV).to(torch.bfloat16)
+    xn = conv.to_ndhwc(x)
+    assert fused.tc_eligible(xn, torch.bfloat16)
+    with torch.no_grad():
+        got = conv.from_ndhwc(fused(xn)).float()
+        w = layer.weight.to(torch.bfloat16).float()
+        want = F.relu(F.batch_norm(F.conv_transpose3d(x.float(), w, None, 2), bn.running_mean,
+                                   bn.running_var, bn.weight, bn.bias, False, 0.0, bn.eps))
+    assert got.shape == want.shape
+    assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-2, atol=1e-3)
