@@ -21,10 +21,7 @@
 // (the store clips partial tiles).  Two accumulators in TMEM (2 x N columns)
 // let the epilogue of tile i overlap the main loop of tile i+1; CTAs are
 // persistent over tiles.
-#include <cuda.h>
-#include <cuda_bf16.h>
-
-#include "ivx_common.cuh"
+#include "ivx_tc_ptx.cuh"
 
 namespace ivx {
 
@@ -53,121 +50,6 @@ struct TcArgs {
     int transposed;
     int up[3];                  // upsampling factor = kernel = stride of the transposed layer
 };
-
-// ------------------------------ PTX wrappers ------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void *p) {
-    return static_cast<uint32_t>(__cvta_generic_to_shared(p));
-}
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(bar), "r"(parity)
-            : "memory");
-    } while (!done);
-}
-
-__device__ __forceinline__ void tma_load_5d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
-                                            int c1, int c2, int c3, int c4) {
-    asm volatile(
-        "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
-        "[%0], [%1, {%3, %4, %5, %6, %7}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-        : "memory");
-}
-
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap *map, uint32_t bar, int c0,
-                                            int c1) {
-    asm volatile(
-        "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes "
-        "[%0], [%1, {%3, %4}], [%2];"
-        ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1)
-        : "memory");
-}
-
-__device__ __forceinline__ void tma_store_5d(const CUtensorMap *map, uint32_t src, int c0, int c1, int c2,
-                                             int c3, int c4) {
-    asm volatile(
-        "cp.async.bulk.tensor.5d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5, %6}], [%1];"
-        ::"l"(map), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4)
-        : "memory");
-}
-
-__device__ __forceinline__ void tmem_alloc(uint32_t slot, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot), "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-
-__device__ __forceinline__ void tmem_dealloc(uint32_t addr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(addr), "r"(cols) : "memory");
-}
-
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                          uint32_t accumulate) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-
-// arrives on the mbarrier once every tcgen05.mma issued so far has completed
-__device__ __forceinline__ void umma_commit(uint32_t bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
-                 : "memory");
-}
-
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]),
-          "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]),
-          "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]),
-          "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-
-// K-major operand tile of 128-byte rows, 128B swizzle: 8-row groups 1024 B apart.
-__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
-    uint64_t d = 0;
-    d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);  // start address, 16-byte units
-    d |= (uint64_t)1 << 16;                      // leading byte offset (unused for swizzled K-major)
-    d |= (uint64_t)(1024 >> 4) << 32;            // stride byte offset between 8-row groups
-    d |= (uint64_t)1 << 46;                      // descriptor version (sm_100)
-    d |= (uint64_t)2 << 61;                      // SWIZZLE_128B
-    return d;
-}
-
-// bf16 x bf16 -> fp32, both operands K-major, M = 128
-__device__ __forceinline__ uint32_t umma_idesc(int n) {
-    return (1u << 4)                      // accumulator format F32
-           | (1u << 7) | (1u << 10)       // A, B format BF16
-           | ((uint32_t)(n >> 3) << 17)   // N
-           | ((uint32_t)(TC_ROWS >> 4) << 24);
-}
 
 struct TileCoord {
     int b, x0, y0, z0, n0;
@@ -369,11 +251,6 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 }
 
 // ------------------------------- host side --------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *,
-                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
-                                  CUtensorMapFloatOOBfill);
-
 static EncodeTiledFn encode_tiled_fn() {
     static EncodeTiledFn fn = nullptr;
     if (fn == nullptr) {
@@ -386,7 +263,7 @@ static EncodeTiledFn encode_tiled_fn() {
     return fn;
 }
 
-static int encode_map(CUtensorMap *map, int rank, void *base, const cuuint64_t *dims,
+int encode_map_bf16(CUtensorMap *map, int rank, void *base, const cuuint64_t *dims,
                       const cuuint64_t *strides_bytes, const cuuint32_t *box, const cuuint32_t *estrides,
                       const char *what) {
     EncodeTiledFn fn = encode_tiled_fn();
@@ -420,6 +297,12 @@ static void pick_box(const int32_t out[3], const int32_t stride[3], int box[3], 
     }
 }
 
+// ivx_conv3d_tc_halo.cu
+double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out);
+int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
+                          const void *weight_bf16, const float *scale, const float *shift,
+                          const void *residual, void *y, cudaStream_t stream);
+
 }  // namespace ivx
 
 using namespace ivx;
@@ -448,6 +331,19 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
     IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
                  reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
                 "tensors must be 16-byte aligned");
+
+    // 3x3x3 stride-1 layers with few output channels are bound by L2->SM traffic in the per-tap
+    // kernel: they go to the halo-reuse kernel (IVX_TC_HALO=0 keeps everything on the per-tap one)
+    {
+        static const bool halo_on = [] {
+            const char *e = getenv("IVX_TC_HALO");
+            return e == nullptr || e[0] != '0';
+        }();
+        int perm[3] = {0, 1, 2}, mt = 1;
+        if (halo_on && p->c_out <= 128 && plan_halo(p, perm, &mt) >= 0.7)
+            return launch_conv3d_tc_halo(p, perm, mt, x, weight_bf16, scale, shift, residual, y,
+                                         (cudaStream_t)stream);
+    }
 
     TcArgs a;
     a.c_in = p->c_in, a.c_out = p->c_out;
@@ -491,7 +387,7 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         const cuuint32_t box[5] = {TC_KCHUNK, (cuuint32_t)(a.box[2] * ld_stride[2]),
                                    (cuuint32_t)(a.box[1] * ld_stride[1]), (cuuint32_t)(a.box[0] * ld_stride[0]), 1};
         const cuuint32_t es[5] = {1, (cuuint32_t)ld_stride[2], (cuuint32_t)ld_stride[1], (cuuint32_t)ld_stride[0], 1};
-        int rc = encode_map(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations");
+        int rc = encode_map_bf16(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations");
         if (rc != IVX_OK) return rc;
     }
     {
@@ -501,7 +397,7 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         const cuuint64_t st[1] = {(cuuint64_t)taps * p->c_in * 2};
         const cuuint32_t box[2] = {TC_KCHUNK, (cuuint32_t)a.n_tile};
         const cuuint32_t es[2] = {1, 1};
-        int rc = encode_map(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights");
+        int rc = encode_map_bf16(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights");
         if (rc != IVX_OK) return rc;
     }
     {
@@ -515,7 +411,7 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         const cuuint32_t box[5] = {64, (cuuint32_t)(a.box[2] * a.up[2]), (cuuint32_t)(a.box[1] * a.up[1]),
                                    (cuuint32_t)(a.box[0] * a.up[0]), 1};
         const cuuint32_t es[5] = {1, (cuuint32_t)a.up[2], (cuuint32_t)a.up[1], (cuuint32_t)a.up[0], 1};
-        int rc = encode_map(&map_y, 5, y, dims, st, box, es, "output");
+        int rc = encode_map_bf16(&map_y, 5, y, dims, st, box, es, "output");
         if (rc != IVX_OK) return rc;
     }
 

@@ -1,0 +1,371 @@
+// 3x3x3 stride-1 Conv3d on tcgen05 with activation-halo reuse.
+//
+// ivx_conv3d_tc.cu re-reads, for each of the 27 taps, a full 128-row activation
+// box and the weight slice through L2; for layers with few channels that L2->SM
+// traffic, not the tensor pipe, is the bound (ncu: ~9.5 TB/s, tensor pipe 18 %
+// at c_in = c_out = 64).  Here the three spatial axes are given roles
+//   P: 8 consecutive outputs  = one 8-row group of the MMA operand,
+//   Q: 16 * MT outputs        = the 16 groups of MT accumulator tiles,
+//   R: 1 output plane,
+// and a CTA loads, per 64-channel chunk and per input plane r-1, r, r+1, ONE box
+// of 16 (P, padded from the 10 needed) x (16*MT + 2) (Q) voxels.  All nine
+// (dP, dQ) taps of that plane are then MMA operands that merely START at a
+// different row of the same box: the 8-row groups stay 16 rows (2048 B) apart;
+// the swizzle is a function of the absolute shared-memory address for both the
+// TMA and the MMA unit, so the shifted start needs nothing else.  One weight slice serves the MT tiles.  Activation traffic
+// drops ~4x and weight traffic MT x compared with the per-tap kernel.
+//
+// Warp roles (224 threads): 0 activation-plane producer, 1 MMA issuer, 2 weight
+// producer, 3..6 epilogue (same fused epilogue / TMA store as the per-tap kernel).
+#include "ivx_tc_ptx.cuh"
+
+namespace ivx {
+
+constexpr int HL_THREADS = 224;
+constexpr int HL_P = 8, HL_PPAD = 16, HL_QT = 16;  // outputs per group, padded box rows along P, groups per tile
+
+struct HaloArgs {
+    int c_in, c_out, n_tile, n_splits;
+    int mt;                    // accumulator tiles per CTA along Q (1 or 2)
+    int dims[3];               // output extent along P, Q, R (== input extent + 2*pad - 2)
+    int pad[3];                // padding along P, Q, R
+    int axis[3];               // tensor axis (0 = X, 1 = Y, 2 = Z) playing role P, Q, R
+    int tiles[3];              // super-tiles along P, Q, R
+    int batch;
+    long long n_tiles;
+    int a_stages, b_stages;
+    long long ostride[3];      // output / residual element strides of one step along P, Q, R
+    long long ostride_b;       // ... and of one batch item
+    int relu, residual_after_act;
+    float post_scale;
+    const float *scale, *shift;
+    const __nv_bfloat16 *res;
+};
+
+struct HaloTile {
+    int b, p0, q0, r0, n0;
+};
+
+__device__ __forceinline__ HaloTile decode_halo_tile(const HaloArgs &a, long long t) {
+    HaloTile c;
+    c.n0 = (int)(t % a.n_splits) * a.n_tile;
+    t /= a.n_splits;
+    c.p0 = (int)(t % a.tiles[0]) * HL_P;
+    t /= a.tiles[0];
+    c.q0 = (int)(t % a.tiles[1]) * (HL_QT * a.mt);
+    t /= a.tiles[1];
+    c.r0 = (int)(t % a.tiles[2]);
+    c.b = (int)(t / a.tiles[2]);
+    return c;
+}
+
+__global__ void __launch_bounds__(HL_THREADS, 1)
+conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
+                      const __grid_constant__ CUtensorMap map_y, const __grid_constant__ HaloArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int plane_rows = HL_PPAD * (HL_QT * a.mt + 2);
+    const int a_bytes = plane_rows * 128;           // multiple of 1024
+    const int b_bytes = a.n_tile * 128;
+    uint8_t *a_base = smem;
+    uint8_t *b_base = a_base + (size_t)a.a_stages * a_bytes;
+    uint8_t *slab_base = b_base + (size_t)a.b_stages * b_bytes;   // 2 output slabs of 128 x 128 B
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + 2 * 128 * 128);
+    uint64_t *a_full = bars, *a_empty = a_full + a.a_stages;
+    uint64_t *b_full = a_empty + a.a_stages, *b_empty = b_full + a.b_stages;
+    uint64_t *acc_full = b_empty + a.b_stages, *acc_empty = acc_full + 2;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int acc_cols = a.mt * a.n_tile;           // columns of one accumulator set
+    const int tmem_cols = 2 * acc_cols <= 32 ? 32 : (2 * acc_cols <= 64 ? 64 : (2 * acc_cols <= 128 ? 128 : (2 * acc_cols <= 256 ? 256 : 512)));
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < a.a_stages; ++s) mbar_init(smem_u32(a_full + s), 1), mbar_init(smem_u32(a_empty + s), 1);
+        for (int s = 0; s < a.b_stages; ++s) mbar_init(smem_u32(b_full + s), 1), mbar_init(smem_u32(b_empty + s), 1);
+        for (int i = 0; i < 2; ++i) mbar_init(smem_u32(acc_full + i), 1), mbar_init(smem_u32(acc_empty + i), 4);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_y) : "memory");
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+    const int k_chunks = a.c_in / 64;
+
+    if (warp == 0) {
+        // -------- activation planes: (chunk, dR) -> one box of 16 x (16*MT + 2) voxels --------
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+                const HaloTile tc = decode_halo_tile(a, t);
+                for (int kc = 0; kc < k_chunks; ++kc)
+                    for (int dr = 0; dr < 3; ++dr) {
+                        mbar_wait(smem_u32(a_empty + stage), phase ^ 1);
+                        const uint32_t bar = smem_u32(a_full + stage);
+                        mbar_expect_tx(bar, (uint32_t)a_bytes);
+                        tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, kc * 64,
+                                    tc.p0 - a.pad[0], tc.q0 - a.pad[1], tc.r0 - a.pad[2] + dr, tc.b);
+                        if (++stage == (uint32_t)a.a_stages) stage = 0, phase ^= 1;
+                    }
+            }
+        }
+    } else if (warp == 2) {
+        // -------- weight slices: (chunk, dR, dP, dQ) -> [n_tile][64] --------
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+                const HaloTile tc = decode_halo_tile(a, t);
+                for (int kc = 0; kc < k_chunks; ++kc)
+                    for (int tap = 0; tap < 27; ++tap) {   // tap = (dR*3 + dQ)*3 + dP in MMA order
+                        const int dp = tap % 3, dq = (tap / 3) % 3, dr = tap / 9;
+                        int k3[3];                          // tap along the tensor axes X, Y, Z
+                        k3[a.axis[0]] = dp, k3[a.axis[1]] = dq, k3[a.axis[2]] = dr;
+                        mbar_wait(smem_u32(b_empty + stage), phase ^ 1);
+                        const uint32_t bar = smem_u32(b_full + stage);
+                        mbar_expect_tx(bar, (uint32_t)b_bytes);
+                        // weights stay packed [c_out][kX][kY][kZ][c_in], as for the per-tap kernel
+                        const int wtap = (k3[0] * 3 + k3[1]) * 3 + k3[2];
+                        tma_load_2d(smem_u32(b_base + (size_t)stage * b_bytes), &map_w, bar,
+                                    wtap * a.c_in + kc * 64, tc.n0);
+                        if (++stage == (uint32_t)a.b_stages) stage = 0, phase ^= 1;
+                    }
+            }
+        }
+    } else if (warp == 1) {
+        // ------------------------------ MMA issuer ------------------------------
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc(a.n_tile);
+            uint32_t sa = 0, pa = 0, sb = 0, pb = 0, acc = 0, acc_phase = 0;
+            for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+                mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t d_tmem = tmem_base + acc * acc_cols;
+                bool first = true;
+                for (int kc = 0; kc < k_chunks; ++kc)
+                    for (int dr = 0; dr < 3; ++dr) {
+                        mbar_wait(smem_u32(a_full + sa), pa);
+                        const uint32_t plane = smem_u32(a_base + (size_t)sa * a_bytes);
+                        for (int dq = 0; dq < 3; ++dq)
+                            for (int dp = 0; dp < 3; ++dp) {
+                                mbar_wait(smem_u32(b_full + sb), pb);
+                                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                                const uint64_t db = umma_desc_sw128(smem_u32(b_base + (size_t)sb * b_bytes));
+                                for (int mt = 0; mt < a.mt; ++mt) {
+                                    // first row of tile mt for this tap: q = mt*16 + dq, p = dp
+                                    const uint32_t row0 = (uint32_t)((mt * HL_QT + dq) * HL_PPAD + dp);
+                                    const uint64_t da = umma_desc_sw128(plane + row0 * 128, HL_PPAD * 128);
+#pragma unroll
+                                    for (int k = 0; k < 4; ++k)
+                                        umma_bf16(d_tmem + mt * a.n_tile, da + 2 * k, db + 2 * k, idesc,
+                                                  !(first && k == 0));
+                                }
+                                first = false;
+                                umma_commit(smem_u32(b_empty + sb));
+                                if (++sb == (uint32_t)a.b_stages) sb = 0, pb ^= 1;
+                            }
+                        umma_commit(smem_u32(a_empty + sa));
+                        if (++sa == (uint32_t)a.a_stages) sa = 0, pa ^= 1;
+                    }
+                umma_commit(smem_u32(acc_full + acc));
+                if (++acc == 2) acc = 0, acc_phase ^= 1;
+            }
+        }
+    } else {
+        // ------------------------------ epilogue (warps 3..6) ------------------------------
+        const int q4 = warp & 3;                // TMEM lane quarter of this warp
+        const int row = q4 * 32 + lane;         // accumulator row = g * 8 + i
+        const int gi = row >> 3, ii = row & 7;  // group (Q offset) and row in group (P offset)
+        const bool epi_leader = (warp == 3 && lane == 0);
+        uint32_t acc = 0, acc_phase = 0;
+        int slab = 0;
+        for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+            const HaloTile tc = decode_halo_tile(a, t);
+            mbar_wait(smem_u32(acc_full + acc), acc_phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            for (int mt = 0; mt < a.mt; ++mt) {
+                const int op = tc.p0 + ii, oq = tc.q0 + mt * HL_QT + gi;
+                const bool row_ok = op < a.dims[0] && oq < a.dims[1];
+                const long long ooff = tc.b * a.ostride_b + op * a.ostride[0] + oq * a.ostride[1] +
+                                       tc.r0 * a.ostride[2];
+                for (int c0 = 0; c0 < a.n_tile; c0 += 64) {
+                    uint8_t *slab_ptr = slab_base + slab * (128 * 128);
+                    if (epi_leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    for (int h = 0; h < 64; h += 32) {
+                        uint32_t v[32];
+                        tmem_ld32(tmem_base + acc * acc_cols + mt * a.n_tile + ((uint32_t)(q4 * 32) << 16) + c0 + h, v);
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                        const int ch = tc.n0 + c0 + h;
+#pragma unroll
+                        for (int j = 0; j < 32; j += 8) {
+                            float f[8];
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                const float sc = a.scale ? __ldg(a.scale + ch + j + e) : 1.f;
+                                const float sh = a.shift ? __ldg(a.shift + ch + j + e) : 0.f;
+                                f[e] = fmaf(__uint_as_float(v[j + e]), sc, sh);
+                            }
+                            float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                            if (a.res && row_ok) {
+                                const uint4 u = __ldg(reinterpret_cast<const uint4 *>(a.res + ooff + ch + j));
+                                const __nv_bfloat162 *p2 = reinterpret_cast<const __nv_bfloat162 *>(&u);
+#pragma unroll
+                                for (int e = 0; e < 4; ++e) {
+                                    const float2 fr = __bfloat1622float2(p2[e]);
+                                    r[2 * e] = fr.x, r[2 * e + 1] = fr.y;
+                                }
+                            }
+#pragma unroll
+                            for (int e = 0; e < 8; ++e) {
+                                if (a.res && !a.residual_after_act) f[e] += r[e];
+                                if (a.relu) f[e] = fmaxf(f[e], 0.f);
+                                if (a.res && a.residual_after_act) f[e] += r[e];
+                                f[e] *= a.post_scale;
+                            }
+                            uint4 o;
+                            __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
+                            __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
+                            o.x = *reinterpret_cast<uint32_t *>(&b0), o.y = *reinterpret_cast<uint32_t *>(&b1);
+                            o.z = *reinterpret_cast<uint32_t *>(&b2), o.w = *reinterpret_cast<uint32_t *>(&b3);
+                            const int chunk = (h + j) >> 3;
+                            *reinterpret_cast<uint4 *>(slab_ptr + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+                        }
+                    }
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                    if (epi_leader) {
+                        tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.p0, tc.q0 + mt * HL_QT, tc.r0, tc.b);
+                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    }
+                    slab ^= 1;
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(acc_empty + acc));
+            if (++acc == 2) acc = 0, acc_phase ^= 1;
+        }
+        if (epi_leader) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+// Decide whether (and how) the halo kernel takes a layer.  perm[role] = tensor axis (0=X,1=Y,2=Z)
+// playing role P, Q, R.  Returns the fraction of accumulator rows that hold real outputs, or 0.
+double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
+    if (p->transposed || p->c_in % 64 != 0 || p->c_out % 64 != 0) return 0.0;
+    for (int d = 0; d < 3; ++d)
+        if (p->kernel[d] != 3 || p->stride[d] != 1 || p->pad[d] > 1) return 0.0;
+    const int n_tile = p->c_out % 128 == 0 ? 128 : 64;
+    (void)n_tile;
+    double best = 0.0;
+    for (int P = 0; P < 3; ++P)
+        for (int Q = 0; Q < 3; ++Q) {
+            if (Q == P) continue;
+            const int R = 3 - P - Q;
+            for (int mt = 1; mt <= 2; ++mt) {
+                const long long tp = (p->out_dims[P] + HL_P - 1) / HL_P;
+                const long long tq = (p->out_dims[Q] + HL_QT * mt - 1) / (HL_QT * mt);
+                double eff = (double)p->out_dims[P] * p->out_dims[Q] / (double)(tp * HL_P * tq * HL_QT * mt);
+                // sharing a weight slice between two tiles is worth a few wasted rows;
+                // P along the contiguous Z axis keeps the TMA rows contiguous in memory
+                const double score = eff * (mt == 2 ? 1.12 : 1.0) * (P == 2 ? 1.02 : 1.0);
+                if (score > best) {
+                    best = score;
+                    perm[0] = P, perm[1] = Q, perm[2] = R;
+                    *mt_out = mt;
+                }
+            }
+        }
+    // report the plain efficiency of the chosen plan
+    const long long tp = (p->out_dims[perm[0]] + HL_P - 1) / HL_P;
+    const long long tq = (p->out_dims[perm[1]] + HL_QT * *mt_out - 1) / (HL_QT * *mt_out);
+    return (double)p->out_dims[perm[0]] * p->out_dims[perm[1]] / (double)(tp * HL_P * tq * HL_QT * *mt_out);
+}
+
+int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
+                          const void *weight_bf16, const float *scale, const float *shift,
+                          const void *residual, void *y, cudaStream_t stream) {
+    HaloArgs a;
+    a.c_in = p->c_in, a.c_out = p->c_out;
+    a.n_tile = p->c_out % 128 == 0 ? 128 : 64;
+    a.n_splits = p->c_out / a.n_tile;
+    a.mt = mt;
+    a.batch = p->batch;
+    // element strides of the channels-last tensors along X, Y, Z
+    const long long in_s[3] = {(long long)p->in_dims[1] * p->in_dims[2] * p->c_in,
+                               (long long)p->in_dims[2] * p->c_in, (long long)p->c_in};
+    const long long out_s[3] = {(long long)p->out_dims[1] * p->out_dims[2] * p->c_out,
+                                (long long)p->out_dims[2] * p->c_out, (long long)p->c_out};
+    for (int r = 0; r < 3; ++r) {
+        a.dims[r] = p->out_dims[perm[r]];
+        a.pad[r] = p->pad[perm[r]];
+        a.axis[r] = perm[r];
+        a.ostride[r] = out_s[perm[r]];
+    }
+    a.ostride_b = out_s[0] * p->out_dims[0];
+    a.tiles[0] = (a.dims[0] + HL_P - 1) / HL_P;
+    a.tiles[1] = (a.dims[1] + HL_QT * mt - 1) / (HL_QT * mt);
+    a.tiles[2] = a.dims[2];
+    a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
+    a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
+    a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
+    const int plane_rows = HL_PPAD * (HL_QT * mt + 2);
+    const int a_bytes = plane_rows * 128, b_bytes = a.n_tile * 128;
+    const int fixed = 2 * 128 * 128 + 1024 + 1024;
+    a.a_stages = 2;
+    a.b_stages = (227 * 1024 - fixed - a.a_stages * a_bytes) / b_bytes;
+    if (a.b_stages > 6) a.b_stages = 6;
+    if (a.b_stages < 2) return fail(IVX_ERR_UNSUPPORTED, "halo kernel: not enough shared memory");
+    // spend what is left on a third plane stage
+    if (227 * 1024 - fixed - 3 * a_bytes - a.b_stages * b_bytes >= 0) a.a_stages = 3;
+    const size_t smem = (size_t)a.a_stages * a_bytes + (size_t)a.b_stages * b_bytes + fixed;
+
+    alignas(64) CUtensorMap map_x, map_w, map_y;
+    {
+        const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[perm[0]],
+                                    (cuuint64_t)p->in_dims[perm[1]], (cuuint64_t)p->in_dims[perm[2]],
+                                    (cuuint64_t)p->batch};
+        const cuuint64_t st[4] = {(cuuint64_t)in_s[perm[0]] * 2, (cuuint64_t)in_s[perm[1]] * 2,
+                                  (cuuint64_t)in_s[perm[2]] * 2, (cuuint64_t)in_s[0] * p->in_dims[0] * 2};
+        const cuuint32_t box[5] = {64, HL_PPAD, (cuuint32_t)(HL_QT * mt + 2), 1, 1};
+        const cuuint32_t es[5] = {1, 1, 1, 1, 1};
+        int rc = encode_map_bf16(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations (halo)");
+        if (rc != IVX_OK) return rc;
+    }
+    {
+        const cuuint64_t dims[2] = {(cuuint64_t)27 * p->c_in, (cuuint64_t)p->c_out};
+        const cuuint64_t st[1] = {(cuuint64_t)27 * p->c_in * 2};
+        const cuuint32_t box[2] = {64, (cuuint32_t)a.n_tile};
+        const cuuint32_t es[2] = {1, 1};
+        int rc = encode_map_bf16(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights (halo)");
+        if (rc != IVX_OK) return rc;
+    }
+    {
+        const cuuint64_t dims[5] = {(cuuint64_t)p->c_out, (cuuint64_t)a.dims[0], (cuuint64_t)a.dims[1],
+                                    (cuuint64_t)a.dims[2], (cuuint64_t)p->batch};
+        const cuuint64_t st[4] = {(cuuint64_t)a.ostride[0] * 2, (cuuint64_t)a.ostride[1] * 2,
+                                  (cuuint64_t)a.ostride[2] * 2, (cuuint64_t)a.ostride_b * 2};
+        const cuuint32_t box[5] = {64, HL_P, HL_QT, 1, 1};
+        const cuuint32_t es[5] = {1, 1, 1, 1, 1};
+        int rc = encode_map_bf16(&map_y, 5, y, dims, st, box, es, "output (halo)");
+        if (rc != IVX_OK) return rc;
+    }
+    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             (int)smem),
+                        "cudaFuncSetAttribute");
+    if (rc != IVX_OK) return rc;
+    const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
+    conv3d_tc_halo_kernel<<<grid, HL_THREADS, smem, stream>>>(map_x, map_w, map_y, a);
+    IVX_CHECK_LAUNCH("conv3d_tc_halo launch");
+    return IVX_OK;
+}
+
+}  // namespace ivx

@@ -26,6 +26,13 @@ CASES = [
     (256, 128, (10, 10, 16), 3, 1, 1, 1),
     (256, 512, (8, 8, 4), 1, 2, 0, 1),
     (128, 64, (8, 8, 8), 1, 1, 0, 1),
+    # shapes the halo-reuse kernel takes (3x3x3, stride 1, c_out <= 128, well-filled tiles)
+    (64, 64, (16, 32, 6), 3, 1, 1, 1),
+    (64, 128, (5, 24, 32), 3, 1, 1, 2),
+    (128, 128, (40, 7, 16), 3, 1, 1, 1),
+    (128, 64, (18, 34, 3), 3, 1, (1, 1, 0), 1),
+    (64, 64, (20, 50, 4), 3, 1, 0, 1),
+    (192, 64, (12, 248, 3), 3, 1, 1, 1),
 ]
 
 
