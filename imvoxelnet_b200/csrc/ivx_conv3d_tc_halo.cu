@@ -8,9 +8,9 @@
 //   Q: 16 * MT outputs        = the 16 groups of MT accumulator tiles,
 //   R: 1 output plane,
 // and a CTA loads, per 64-channel chunk and per input plane r-1, r, r+1, ONE box
-// of 16 (P, padded from the 10 needed) x (16*MT + 2) (Q) voxels.  All nine
-// (dP, dQ) taps of that plane are then MMA operands that merely START at a
-// different row of the same box: the 8-row groups stay 16 rows (2048 B) apart;
+// of 10 (P: 8 + halo) x (16*MT + 2) (Q) voxels.  All nine (dP, dQ) taps of that
+// plane are then MMA operands that merely START at a different row of the same
+// box: the 8-row groups stay 10 rows (1280 B) apart;
 // the swizzle is a function of the absolute shared-memory address for both the
 // TMA and the MMA unit, so the shifted start needs nothing else.  One weight slice serves the MT tiles.  Activation traffic
 // drops ~4x and weight traffic MT x compared with the per-tap kernel.
@@ -22,7 +22,7 @@
 namespace ivx {
 
 constexpr int HL_THREADS = 224;
-constexpr int HL_P = 8, HL_PPAD = 16, HL_QT = 16;  // outputs per group, padded box rows along P, groups per tile
+constexpr int HL_P = 8, HL_PPAD = 10, HL_QT = 16;  // outputs per group, box rows along P (8 + halo), groups per tile
 
 struct HaloArgs {
     int c_in, c_out, n_tile, n_splits;
@@ -65,7 +65,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int plane_rows = HL_PPAD * (HL_QT * a.mt + 2);
-    const int a_bytes = plane_rows * 128;           // multiple of 1024
+    const int a_bytes = (plane_rows * 128 + 1023) & ~1023;   // stage pitch; the box itself is plane_rows * 128
     const int b_bytes = a.n_tile * 128;
     uint8_t *a_base = smem;
     uint8_t *b_base = a_base + (size_t)a.a_stages * a_bytes;
@@ -97,7 +97,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     const int k_chunks = a.c_in / 64;
 
     if (warp == 0) {
-        // -------- activation planes: (chunk, dR) -> one box of 16 x (16*MT + 2) voxels --------
+        // -------- activation planes: (chunk, dR) -> one box of 10 x (16*MT + 2) voxels --------
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
@@ -106,7 +106,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                     for (int dr = 0; dr < 3; ++dr) {
                         mbar_wait(smem_u32(a_empty + stage), phase ^ 1);
                         const uint32_t bar = smem_u32(a_full + stage);
-                        mbar_expect_tx(bar, (uint32_t)a_bytes);
+                        mbar_expect_tx(bar, (uint32_t)(plane_rows * 128));
                         tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, kc * 64,
                                     tc.p0 - a.pad[0], tc.q0 - a.pad[1], tc.r0 - a.pad[2] + dr, tc.b);
                         if (++stage == (uint32_t)a.a_stages) stage = 0, phase ^= 1;
@@ -318,14 +318,14 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
     a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
     const int plane_rows = HL_PPAD * (HL_QT * mt + 2);
-    const int a_bytes = plane_rows * 128, b_bytes = a.n_tile * 128;
+    const int a_bytes = (plane_rows * 128 + 1023) & ~1023, b_bytes = a.n_tile * 128;
     const int fixed = 2 * 128 * 128 + 1024 + 1024;
-    a.a_stages = 2;
-    a.b_stages = (227 * 1024 - fixed - a.a_stages * a_bytes) / b_bytes;
-    if (a.b_stages > 6) a.b_stages = 6;
-    if (a.b_stages < 2) return fail(IVX_ERR_UNSUPPORTED, "halo kernel: not enough shared memory");
-    // spend what is left on a third plane stage
-    if (227 * 1024 - fixed - 3 * a_bytes - a.b_stages * b_bytes >= 0) a.a_stages = 3;
+    // weight slices: enough stages to cover a plane's nine taps ahead of time when they are
+    // small, the rest of the shared memory goes to activation planes (each feeds 36*MT MMAs)
+    a.b_stages = b_bytes <= 8192 ? 6 : 4;
+    a.a_stages = (227 * 1024 - fixed - a.b_stages * b_bytes) / a_bytes;
+    if (a.a_stages > 4) a.a_stages = 4;
+    if (a.a_stages < 2) return fail(IVX_ERR_UNSUPPORTED, "halo kernel: not enough shared memory");
     const size_t smem = (size_t)a.a_stages * a_bytes + (size_t)a.b_stages * b_bytes + fixed;
 
     alignas(64) CUtensorMap map_x, map_w, map_y;
