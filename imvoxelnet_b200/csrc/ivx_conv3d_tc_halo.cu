@@ -15,8 +15,17 @@
 // TMA and the MMA unit, so the shifted start needs nothing else.  One weight slice serves the MT tiles.  Activation traffic
 // drops ~4x and weight traffic MT x compared with the per-tap kernel.
 //
+// Operand roles are SWAPPED relative to the per-tap kernel: the weight slice is the MMA's
+// A operand (M = 128 accumulator lanes = output channels; a 64-channel layer leaves
+// the upper lanes unused) and the voxels are the N dimension (N = 128 * MT).  Measured
+// on B200, one tcgen05.mma with M = 128 costs >= ~128 cycles whatever N is (the A
+// operand read), so N = 64/128-channel layers ran at 25 % / 50 % of the tensor peak
+// with channels on N; with 256 voxels on N they run at the full M = 128 rate.  The
+// accumulator is therefore D^T (lane = channel, column = voxel): the epilogue has the
+// folded BN scale/shift as per-thread constants and transposes through shared memory.
+//
 // Warp roles (224 threads): 0 activation-plane producer, 1 MMA issuer, 2 weight
-// producer, 3..6 epilogue (same fused epilogue / TMA store as the per-tap kernel).
+// producer, 3..6 epilogue.
 #include "ivx_tc_ptx.cuh"
 
 namespace ivx {
@@ -33,13 +42,14 @@ struct HaloArgs {
     int tiles[3];              // super-tiles along P, Q, R
     int batch;
     long long n_tiles;
-    int a_stages, b_stages;
+    int a_stages, b_stages, n_slabs;
     long long ostride[3];      // output / residual element strides of one step along P, Q, R
     long long ostride_b;       // ... and of one batch item
     int relu, residual_after_act;
     float post_scale;
     const float *scale, *shift;
     const __nv_bfloat16 *res;
+    int debug;                 // experiments: 1 = epilogue does no work, 2 = no MMA is issued
 };
 
 struct HaloTile {
@@ -61,33 +71,38 @@ __device__ __forceinline__ HaloTile decode_halo_tile(const HaloArgs &a, long lon
 
 __global__ void __launch_bounds__(HL_THREADS, 1)
 conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-                      const __grid_constant__ CUtensorMap map_y, const __grid_constant__ HaloArgs a) {
+                      const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_r,
+                      const __grid_constant__ HaloArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int plane_rows = HL_PPAD * (HL_QT * a.mt + 2);
     const int a_bytes = (plane_rows * 128 + 1023) & ~1023;   // stage pitch; the box itself is plane_rows * 128
-    const int b_bytes = a.n_tile * 128;
+    const int b_bytes = 128 * 128;                  // weight stage: 128 channel rows (n_tile of them loaded)
+    const int w_bytes = a.n_tile * 128;             // bytes one weight load actually writes
     uint8_t *a_base = smem;
     uint8_t *b_base = a_base + (size_t)a.a_stages * a_bytes;
-    uint8_t *slab_base = b_base + (size_t)a.b_stages * b_bytes;   // 2 output slabs of 128 x 128 B
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + 2 * 128 * 128);
+    uint8_t *slab_base = b_base + (size_t)a.b_stages * b_bytes;   // n_slabs output slabs of 128 x 128 B
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + (size_t)a.n_slabs * 128 * 128);
     uint64_t *a_full = bars, *a_empty = a_full + a.a_stages;
     uint64_t *b_full = a_empty + a.a_stages, *b_empty = b_full + a.b_stages;
     uint64_t *acc_full = b_empty + a.b_stages, *acc_empty = acc_full + 2;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+    uint64_t *res_bar = acc_empty + 2;              // residual tile landed in slab set 0 / 1
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(res_bar + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int acc_cols = a.mt * a.n_tile;           // columns of one accumulator set
+    const int acc_cols = a.mt * 128;                // columns (voxels) of one accumulator
     const int tmem_cols = 2 * acc_cols <= 32 ? 32 : (2 * acc_cols <= 64 ? 64 : (2 * acc_cols <= 128 ? 128 : (2 * acc_cols <= 256 ? 256 : 512)));
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < a.a_stages; ++s) mbar_init(smem_u32(a_full + s), 1), mbar_init(smem_u32(a_empty + s), 1);
         for (int s = 0; s < a.b_stages; ++s) mbar_init(smem_u32(b_full + s), 1), mbar_init(smem_u32(b_empty + s), 1);
         for (int i = 0; i < 2; ++i) mbar_init(smem_u32(acc_full + i), 1), mbar_init(smem_u32(acc_empty + i), 4);
+        for (int i = 0; i < 2; ++i) mbar_init(smem_u32(res_bar + i), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_y) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_r) : "memory");
     }
     if (warp == 1) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -126,7 +141,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         k3[a.axis[0]] = dp, k3[a.axis[1]] = dq, k3[a.axis[2]] = dr;
                         mbar_wait(smem_u32(b_empty + stage), phase ^ 1);
                         const uint32_t bar = smem_u32(b_full + stage);
-                        mbar_expect_tx(bar, (uint32_t)b_bytes);
+                        mbar_expect_tx(bar, (uint32_t)w_bytes);
                         // weights stay packed [c_out][kX][kY][kZ][c_in], as for the per-tap kernel
                         const int wtap = (k3[0] * 3 + k3[1]) * 3 + k3[2];
                         tma_load_2d(smem_u32(b_base + (size_t)stage * b_bytes), &map_w, bar,
@@ -138,7 +153,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     } else if (warp == 1) {
         // ------------------------------ MMA issuer ------------------------------
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc(a.n_tile);
+            const uint32_t idesc = umma_idesc(128 * a.mt);   // M = 128 channel lanes, N = voxels
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0, acc = 0, acc_phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
                 mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
@@ -153,15 +168,15 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                             for (int dp = 0; dp < 3; ++dp) {
                                 mbar_wait(smem_u32(b_full + sb), pb);
                                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                                const uint64_t db = umma_desc_sw128(smem_u32(b_base + (size_t)sb * b_bytes));
-                                for (int mt = 0; mt < a.mt; ++mt) {
-                                    // first row of tile mt for this tap: q = mt*16 + dq, p = dp
-                                    const uint32_t row0 = (uint32_t)((mt * HL_QT + dq) * HL_PPAD + dp);
-                                    const uint64_t da = umma_desc_sw128(plane + row0 * 128, HL_PPAD * 128);
+                                // A operand: the weight slice [channel][64]
+                                const uint64_t dw = umma_desc_sw128(smem_u32(b_base + (size_t)sb * b_bytes));
+                                // B operand: 16*MT groups of 8 voxels starting at (q = dq, p = dp) of the plane
+                                const uint32_t row0 = (uint32_t)(dq * HL_PPAD + dp);
+                                const uint64_t dx = umma_desc_sw128(plane + row0 * 128, HL_PPAD * 128);
+                                if (a.debug != 2) {
 #pragma unroll
                                     for (int k = 0; k < 4; ++k)
-                                        umma_bf16(d_tmem + mt * a.n_tile, da + 2 * k, db + 2 * k, idesc,
-                                                  !(first && k == 0));
+                                        umma_bf16(d_tmem, dw + 2 * k, dx + 2 * k, idesc, !(first && k == 0));
                                 }
                                 first = false;
                                 umma_commit(smem_u32(b_empty + sb));
@@ -176,73 +191,86 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         }
     } else {
         // ------------------------------ epilogue (warps 3..6) ------------------------------
-        const int q4 = warp & 3;                // TMEM lane quarter of this warp
-        const int row = q4 * 32 + lane;         // accumulator row = g * 8 + i
-        const int gi = row >> 3, ii = row & 7;  // group (Q offset) and row in group (P offset)
+        // Accumulator lane = output channel, column = voxel row of the tile (group g = col >> 3,
+        // row in group i = col & 7).  A voxel tile is staged as 64-channel slabs of 128 rows x 128 B
+        // (TMA swizzle) and stored by TMA; the residual tile is TMA-loaded into the same slabs
+        // first, so adding it is a read-modify-write of shared memory.
+        const int q4 = warp & 3;                       // TMEM lane quarter of this warp
+        const int ch_local = q4 * 32 + lane;           // channel inside the n-tile
+        const bool ch_ok = ch_local < a.n_tile;
         const bool epi_leader = (warp == 3 && lane == 0);
-        uint32_t acc = 0, acc_phase = 0;
-        int slab = 0;
+        const bool has_res = a.res != nullptr;
+        const int slabs_per_tile = a.n_tile / 64;
+        const int slab_sets = a.n_slabs / slabs_per_tile;
+        const int my_slab = ch_local >> 6, my_chunk = (ch_local & 63) >> 3, my_byte = (ch_local & 7) * 2;
+        uint32_t xoff[8];                              // byte offset inside a slab row, by (row & 7)
+#pragma unroll
+        for (int c = 0; c < 8; ++c) xoff[c] = (uint32_t)(((my_chunk ^ c) << 4) + my_byte);
+        uint32_t acc = 0, acc_phase = 0, res_phase[2] = {0, 0};
+        int set = 0;
+
+        auto slab_free = [&]() {   // leader: the TMA stores that last read slab set `set` are done with it
+            if (slab_sets > 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+        };
+        auto load_residual = [&](const HaloTile &tc, int mt, int into) {   // leader only
+            slab_free();
+            const uint32_t bar = smem_u32(res_bar + into);
+            mbar_expect_tx(bar, (uint32_t)(slabs_per_tile * 128 * 128));
+            for (int sl = 0; sl < slabs_per_tile; ++sl)
+                tma_load_5d(smem_u32(slab_base + (size_t)(into * slabs_per_tile + sl) * (128 * 128)), &map_r, bar,
+                            tc.n0 + sl * 64, tc.p0, tc.q0 + mt * HL_QT, tc.r0, tc.b);
+        };
+
         for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
             const HaloTile tc = decode_halo_tile(a, t);
+            const int ch = tc.n0 + ch_local;
+            const float sc = (a.scale && ch_ok) ? __ldg(a.scale + ch) : 1.f;
+            const float sh = (a.shift && ch_ok) ? __ldg(a.shift + ch) : 0.f;
+            if (has_res && epi_leader) load_residual(tc, 0, set);   // overlaps the wait for the accumulator
             mbar_wait(smem_u32(acc_full + acc), acc_phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            for (int mt = 0; mt < a.mt; ++mt) {
-                const int op = tc.p0 + ii, oq = tc.q0 + mt * HL_QT + gi;
-                const bool row_ok = op < a.dims[0] && oq < a.dims[1];
-                const long long ooff = tc.b * a.ostride_b + op * a.ostride[0] + oq * a.ostride[1] +
-                                       tc.r0 * a.ostride[2];
-                for (int c0 = 0; c0 < a.n_tile; c0 += 64) {
-                    uint8_t *slab_ptr = slab_base + slab * (128 * 128);
-                    if (epi_leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            for (int mt = 0; mt < (a.debug == 1 ? 0 : a.mt); ++mt) {
+                if (has_res) {
+                    if (mt > 0 && epi_leader) load_residual(tc, mt, set);
+                    mbar_wait(smem_u32(res_bar + set), res_phase[set]);
+                    res_phase[set] ^= 1;
+                } else {
+                    if (epi_leader) slab_free();
                     asm volatile("bar.sync 1, 128;" ::: "memory");
-                    for (int h = 0; h < 64; h += 32) {
-                        uint32_t v[32];
-                        tmem_ld32(tmem_base + acc * acc_cols + mt * a.n_tile + ((uint32_t)(q4 * 32) << 16) + c0 + h, v);
-                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                        const int ch = tc.n0 + c0 + h;
+                }
+                uint8_t *my_rows = slab_base + (size_t)(set * slabs_per_tile + my_slab) * (128 * 128);
+                for (int v0 = 0; v0 < 128; v0 += 32) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + acc * acc_cols + mt * 128 + ((uint32_t)(q4 * 32) << 16) + v0, v);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (ch_ok) {
+                        uint8_t *rows = my_rows + v0 * 128;
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            float f[8];
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                const float sc = a.scale ? __ldg(a.scale + ch + j + e) : 1.f;
-                                const float sh = a.shift ? __ldg(a.shift + ch + j + e) : 0.f;
-                                f[e] = fmaf(__uint_as_float(v[j + e]), sc, sh);
+                        for (int j = 0; j < 32; ++j) {
+                            __nv_bfloat16 *cell = reinterpret_cast<__nv_bfloat16 *>(rows + j * 128 + xoff[j & 7]);
+                            float f = fmaf(__uint_as_float(v[j]), sc, sh);
+                            if (has_res) {
+                                const float r = __bfloat162float(*cell);
+                                if (!a.residual_after_act) f += r;
+                                if (a.relu) f = fmaxf(f, 0.f);
+                                if (a.residual_after_act) f += r;
+                            } else if (a.relu) {
+                                f = fmaxf(f, 0.f);
                             }
-                            float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                            if (a.res && row_ok) {
-                                const uint4 u = __ldg(reinterpret_cast<const uint4 *>(a.res + ooff + ch + j));
-                                const __nv_bfloat162 *p2 = reinterpret_cast<const __nv_bfloat162 *>(&u);
-#pragma unroll
-                                for (int e = 0; e < 4; ++e) {
-                                    const float2 fr = __bfloat1622float2(p2[e]);
-                                    r[2 * e] = fr.x, r[2 * e + 1] = fr.y;
-                                }
-                            }
-#pragma unroll
-                            for (int e = 0; e < 8; ++e) {
-                                if (a.res && !a.residual_after_act) f[e] += r[e];
-                                if (a.relu) f[e] = fmaxf(f[e], 0.f);
-                                if (a.res && a.residual_after_act) f[e] += r[e];
-                                f[e] *= a.post_scale;
-                            }
-                            uint4 o;
-                            __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
-                            __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
-                            o.x = *reinterpret_cast<uint32_t *>(&b0), o.y = *reinterpret_cast<uint32_t *>(&b1);
-                            o.z = *reinterpret_cast<uint32_t *>(&b2), o.w = *reinterpret_cast<uint32_t *>(&b3);
-                            const int chunk = (h + j) >> 3;
-                            *reinterpret_cast<uint4 *>(slab_ptr + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+                            *cell = __float2bfloat16_rn(f * a.post_scale);
                         }
                     }
-                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
-                    if (epi_leader) {
-                        tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.p0, tc.q0 + mt * HL_QT, tc.r0, tc.b);
-                        asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-                    }
-                    slab ^= 1;
                 }
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (epi_leader) {
+                    for (int sl = 0; sl < slabs_per_tile; ++sl)
+                        tma_store_5d(&map_y, smem_u32(slab_base + (size_t)(set * slabs_per_tile + sl) * (128 * 128)),
+                                     tc.n0 + sl * 64, tc.p0, tc.q0 + mt * HL_QT, tc.r0, tc.b);
+                    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                }
+                if (++set == slab_sets) set = 0;
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncwarp();
@@ -317,18 +345,29 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
     a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
     a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
+    {
+        const char *e = getenv("IVX_HALO_DEBUG");
+        a.debug = e ? atoi(e) : 0;
+    }
     const int plane_rows = HL_PPAD * (HL_QT * mt + 2);
-    const int a_bytes = (plane_rows * 128 + 1023) & ~1023, b_bytes = a.n_tile * 128;
-    const int fixed = 2 * 128 * 128 + 1024 + 1024;
-    // weight slices: enough stages to cover a plane's nine taps ahead of time when they are
-    // small, the rest of the shared memory goes to activation planes (each feeds 36*MT MMAs)
-    a.b_stages = b_bytes <= 8192 ? 6 : 4;
-    a.a_stages = (227 * 1024 - fixed - a.b_stages * b_bytes) / a_bytes;
+    const int a_bytes = (plane_rows * 128 + 1023) & ~1023, b_bytes = 128 * 128;
+    const int slabs_per_tile = a.n_tile / 64;
+    // shared memory: weight ring (16 KB stages), two sets of output slabs if they fit, the
+    // rest goes to activation planes (each one feeds 36 MMAs)
+    a.b_stages = 4;
+    a.n_slabs = 2 * slabs_per_tile;
+    const int budget = 227 * 1024 - 2048;
+    a.a_stages = (budget - a.b_stages * b_bytes - a.n_slabs * 16384) / a_bytes;
+    if (a.a_stages < 3 && slabs_per_tile == 2) {   // 128-channel tiles: one slab set buys a plane stage
+        a.n_slabs = slabs_per_tile;
+        a.a_stages = (budget - a.b_stages * b_bytes - a.n_slabs * 16384) / a_bytes;
+    }
     if (a.a_stages > 4) a.a_stages = 4;
     if (a.a_stages < 2) return fail(IVX_ERR_UNSUPPORTED, "halo kernel: not enough shared memory");
-    const size_t smem = (size_t)a.a_stages * a_bytes + (size_t)a.b_stages * b_bytes + fixed;
+    const size_t smem = (size_t)a.a_stages * a_bytes + (size_t)a.b_stages * b_bytes +
+                       (size_t)a.n_slabs * 16384 + 2048;
 
-    alignas(64) CUtensorMap map_x, map_w, map_y;
+    alignas(64) CUtensorMap map_x, map_w, map_y, map_r;
     {
         const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[perm[0]],
                                     (cuuint64_t)p->in_dims[perm[1]], (cuuint64_t)p->in_dims[perm[2]],
@@ -357,13 +396,18 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
         const cuuint32_t es[5] = {1, 1, 1, 1, 1};
         int rc = encode_map_bf16(&map_y, 5, y, dims, st, box, es, "output (halo)");
         if (rc != IVX_OK) return rc;
+        map_r = map_y;
+        if (residual != nullptr) {
+            rc = encode_map_bf16(&map_r, 5, const_cast<void *>(residual), dims, st, box, es, "residual (halo)");
+            if (rc != IVX_OK) return rc;
+        }
     }
     int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem),
                         "cudaFuncSetAttribute");
     if (rc != IVX_OK) return rc;
     const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
-    conv3d_tc_halo_kernel<<<grid, HL_THREADS, smem, stream>>>(map_x, map_w, map_y, a);
+    conv3d_tc_halo_kernel<<<grid, HL_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
     IVX_CHECK_LAUNCH("conv3d_tc_halo launch");
     return IVX_OK;
 }
