@@ -332,15 +332,22 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
                  reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
                 "tensors must be 16-byte aligned");
 
-    // 3x3x3 stride-1 layers with few output channels are bound by L2->SM traffic in the per-tap
-    // kernel: they go to the halo-reuse kernel (IVX_TC_HALO=0 keeps everything on the per-tap one)
+    // 3x3x3 layers (stride 1, or a stride along one axis) whose grid fills the 8 x 16*MT tiles
+    // go to the halo-reuse kernel (IVX_TC_HALO=0 keeps everything on the per-tap one)
     {
         static const bool halo_on = [] {
             const char *e = getenv("IVX_TC_HALO");
             return e == nullptr || e[0] != '0';
         }();
+        static const int halo_max_cout = [] {
+            const char *e = getenv("IVX_HALO_MAX_COUT");
+            return e ? atoi(e) : 1024;
+        }();
         int perm[3] = {0, 1, 2}, mt = 1;
-        if (halo_on && p->c_out <= 128 && plan_halo(p, perm, &mt) >= 0.7)
+        // with one tile per CTA (mt == 1) an MMA covers only 128 voxels, i.e. half the tensor rate:
+        // still a win for <= 128 channels (the per-tap kernel is at half rate there too), not above
+        if (halo_on && p->c_out <= halo_max_cout && plan_halo(p, perm, &mt) >= 0.7 &&
+            (mt == 2 || p->c_out <= 128))
             return launch_conv3d_tc_halo(p, perm, mt, x, weight_bf16, scale, shift, residual, y,
                                          (cudaStream_t)stream);
     }

@@ -38,6 +38,7 @@ struct HaloArgs {
     int mt;                    // accumulator tiles per CTA along Q (1 or 2)
     int dims[3];               // output extent along P, Q, R (== input extent + 2*pad - 2)
     int pad[3];                // padding along P, Q, R
+    int stride_r;              // conv stride along R (P and Q are stride 1)
     int axis[3];               // tensor axis (0 = X, 1 = Y, 2 = Z) playing role P, Q, R
     int tiles[3];              // super-tiles along P, Q, R
     int batch;
@@ -123,7 +124,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         const uint32_t bar = smem_u32(a_full + stage);
                         mbar_expect_tx(bar, (uint32_t)(plane_rows * 128));
                         tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, kc * 64,
-                                    tc.p0 - a.pad[0], tc.q0 - a.pad[1], tc.r0 - a.pad[2] + dr, tc.b);
+                                    tc.p0 - a.pad[0], tc.q0 - a.pad[1], tc.r0 * a.stride_r - a.pad[2] + dr, tc.b);
                         if (++stage == (uint32_t)a.a_stages) stage = 0, phase ^= 1;
                     }
             }
@@ -213,8 +214,10 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             if (slab_sets > 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
             else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
         };
-        auto load_residual = [&](const HaloTile &tc, int mt, int into) {   // leader only
-            slab_free();
+        // leader only.  `pending` = TMA stores that may still be reading OTHER slab sets
+        auto load_residual = [&](const HaloTile &tc, int mt, int into, int pending) {
+            if (pending >= 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+            else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
             const uint32_t bar = smem_u32(res_bar + into);
             mbar_expect_tx(bar, (uint32_t)(slabs_per_tile * 128 * 128));
             for (int sl = 0; sl < slabs_per_tile; ++sl)
@@ -227,12 +230,19 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             const int ch = tc.n0 + ch_local;
             const float sc = (a.scale && ch_ok) ? __ldg(a.scale + ch) : 1.f;
             const float sh = (a.shift && ch_ok) ? __ldg(a.shift + ch) : 0.f;
-            if (has_res && epi_leader) load_residual(tc, 0, set);   // overlaps the wait for the accumulator
+            // residual tiles are fetched while the accumulator is still being produced: all of the
+            // super-tile's when every tile has a slab set of its own, else only the first
+            const bool res_ahead = slab_sets >= a.mt;
+            if (has_res && epi_leader) {
+                load_residual(tc, 0, set, slab_sets - 1);
+                if (res_ahead)
+                    for (int mt = 1; mt < a.mt; ++mt) load_residual(tc, mt, (set + mt) % slab_sets, slab_sets - 1 - mt);
+            }
             mbar_wait(smem_u32(acc_full + acc), acc_phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             for (int mt = 0; mt < (a.debug == 1 ? 0 : a.mt); ++mt) {
                 if (has_res) {
-                    if (mt > 0 && epi_leader) load_residual(tc, mt, set);
+                    if (mt > 0 && !res_ahead && epi_leader) load_residual(tc, mt, set, slab_sets - 1);
                     mbar_wait(smem_u32(res_bar + set), res_phase[set]);
                     res_phase[set] ^= 1;
                 } else {
@@ -289,15 +299,20 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
 // playing role P, Q, R.  Returns the fraction of accumulator rows that hold real outputs, or 0.
 double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
     if (p->transposed || p->c_in % 64 != 0 || p->c_out % 64 != 0) return 0.0;
-    for (int d = 0; d < 3; ++d)
-        if (p->kernel[d] != 3 || p->stride[d] != 1 || p->pad[d] > 1) return 0.0;
-    const int n_tile = p->c_out % 128 == 0 ? 128 : 64;
-    (void)n_tile;
+    int strided_axis = -1;
+    for (int d = 0; d < 3; ++d) {
+        if (p->kernel[d] != 3 || p->pad[d] > 1) return 0.0;
+        if (p->stride[d] != 1) {
+            if (strided_axis >= 0) return 0.0;   // a stride is only supported along R (one axis)
+            strided_axis = d;
+        }
+    }
     double best = 0.0;
     for (int P = 0; P < 3; ++P)
         for (int Q = 0; Q < 3; ++Q) {
             if (Q == P) continue;
             const int R = 3 - P - Q;
+            if (strided_axis >= 0 && R != strided_axis) continue;
             for (int mt = 1; mt <= 2; ++mt) {
                 const long long tp = (p->out_dims[P] + HL_P - 1) / HL_P;
                 const long long tq = (p->out_dims[Q] + HL_QT * mt - 1) / (HL_QT * mt);
@@ -312,6 +327,7 @@ double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
                 }
             }
         }
+    if (best == 0.0) return 0.0;
     // report the plain efficiency of the chosen plan
     const long long tp = (p->out_dims[perm[0]] + HL_P - 1) / HL_P;
     const long long tq = (p->out_dims[perm[1]] + HL_QT * *mt_out - 1) / (HL_QT * *mt_out);
@@ -339,6 +355,7 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
         a.ostride[r] = out_s[perm[r]];
     }
     a.ostride_b = out_s[0] * p->out_dims[0];
+    a.stride_r = p->stride[perm[2]];
     a.tiles[0] = (a.dims[0] + HL_P - 1) / HL_P;
     a.tiles[1] = (a.dims[1] + HL_QT * mt - 1) / (HL_QT * mt);
     a.tiles[2] = a.dims[2];

@@ -222,7 +222,10 @@ class EncoderDecoder(nn.Module):
         feats = feats[::-1]
         outs = []
         for i in range(len(self.layers_up_conv)):
-            x = self._up[i](upsample2x_trilinear(x))                     # :359-360
+            # :359-360 computes conv1x1x1(upsample(x)); a bias-free pointwise conv and trilinear
+            # interpolation (weights summing to 1) commute, so the conv runs on the 8x smaller
+            # tensor and the up-sampling on the narrower one
+            x = upsample2x_trilinear(self._up[i](x))
             # (x + relu(bn(conv(skip)))) / 2  (:366-367) in the projection's epilogue
             x = self.proj[i]._f(feats[i + 1], residual=x, residual_after_act=True, post_scale=0.5)
             x = self.layers_up_res[i](x)

@@ -33,6 +33,11 @@ CASES = [
     (128, 64, (18, 34, 3), 3, 1, (1, 1, 0), 1),
     (64, 64, (20, 50, 4), 3, 1, 0, 1),
     (192, 64, (12, 248, 3), 3, 1, 1, 1),
+    (64, 128, (16, 32, 12), 3, (1, 1, 2), 1, 1),
+    (128, 256, (8, 32, 6), 3, (1, 1, 2), 1, 2),
+    (64, 64, (13, 16, 32), 3, (2, 1, 1), 1, 1),
+    (256, 256, (16, 16, 3), 3, 1, 0, 1),
+    (128, 512, (8, 32, 4), 3, 1, 1, 1),
 ]
 
 
