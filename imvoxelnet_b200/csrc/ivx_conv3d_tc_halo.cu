@@ -50,7 +50,7 @@ struct HaloArgs {
     float post_scale;
     const float *scale, *shift;
     const __nv_bfloat16 *res;
-    int debug;                 // experiments: 1 = epilogue does no work, 2 = no MMA is issued
+    int debug;                 // IVX_HALO_DEBUG: 1 = epilogue does no work, 2 = no MMA issued (timing decomposition only)
 };
 
 struct HaloTile {

@@ -110,3 +110,41 @@ def test_neck_bf16_mode(name):
         err = (a.float() - b).abs().max().item() / b.abs().max().item()
         print(name, tuple(b.shape), "bf16 max err / max|ref| = %.4f" % err)
         assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
+
+
+def test_kitti_neck_at_full_size_both_precisions():
+    """BASELINE.json configs[1] grid (216x248x12, 64 channels), one scene: the
+    drop-in neck against the oracle run by cuDNN in fp32 (TF32 off)."""
+    kw = dict(in_channels=64, out_channels=256)
+    torch.manual_seed(3)
+    ref = torch_necks.KittiImVoxelNeck(**kw).eval()
+    torch_necks.randomize_norms(ref, 9)
+    m = necks.KittiImVoxelNeck(**kw).eval()
+    m.load_state_dict(ref.state_dict())
+    ref.to(DEV), m.to(DEV)
+    x = torch.randn(1, 64, 216, 248, 12, device=DEV)
+    with torch.no_grad():
+        want = ref(x)[0]
+        got32 = m(x)[0]
+        m.precision = "bf16"
+        got16 = m(x.contiguous(memory_format=torch.channels_last_3d))[0]
+    assert got32.shape == want.shape == (1, 256, 246, 214)
+    assert_volume_close(got32.cpu().numpy(), want.cpu().numpy())
+    assert_volume_close(got16.float().cpu().numpy(), want.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
+
+
+def test_fast_indoor_neck_at_full_size_bf16():
+    kw = dict(in_channels=256, n_blocks=[1, 1, 1], out_channels=128)
+    torch.manual_seed(4)
+    ref = torch_necks.FastIndoorImVoxelNeck(**kw).eval()
+    torch_necks.randomize_norms(ref, 10)
+    m = necks.FastIndoorImVoxelNeck(**kw).eval()
+    m.load_state_dict(ref.state_dict())
+    m.precision = "bf16"
+    ref.to(DEV), m.to(DEV)
+    x = torch.randn(2, 256, 40, 40, 16, device=DEV)
+    with torch.no_grad():
+        want = ref(x)
+        got = m(x)
+    for a, b in zip(got, want):
+        assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
