@@ -321,3 +321,29 @@ def test_nchw_workspace_is_checked():
     assert lib.ivx_backproject_scenes_nchw(*args, ws.data_ptr(), need, None) == 0
     torch.cuda.synchronize()
     assert torch.count_nonzero(vol) == 0
+
+
+def test_streamed_hot_path_equals_serial_calls():
+    """Copies on side streams, double-buffered: same results as plain calls."""
+    from imvoxelnet_b200.pipeline import StreamedHotPath
+    sc, full, origin, P = _scene_inputs("sunrgbd_fast", seed=31)
+    h, w = sc.feat_hw
+    hws, origins = [(h, w)] * 2, [origin] * 2
+
+    def compute(feats, proj):
+        vol, valid, _ = ops.backproject_scenes(feats, hws, proj, sc.n_voxels, sc.voxel_size, origins)
+        return [vol], valid
+
+    batches = []
+    for i in range(5):
+        f = scenes.random_features(sc, seed=40 + i, batch=2, channels_last=True)
+        pinned = StreamedHotPath._pinned_like(f)
+        pinned.copy_(f)
+        batches.append((pinned, torch.stack([P, P]).pin_memory()))
+    runner = StreamedHotPath(compute)
+    n = 0
+    for i, (outs, valid) in enumerate(runner.run(iter(batches))):
+        ref_outs, ref_valid = compute(batches[i][0].to(DEV), batches[i][1].to(DEV))
+        assert torch.equal(outs[0], ref_outs[0].cpu()) and torch.equal(valid, ref_valid.cpu())
+        n += 1
+    assert n == 5
