@@ -87,14 +87,18 @@ __device__ __forceinline__ float dot4_rn(const float *P, float x, float y, float
 // pixel coordinates as floats (exact integers when valid).
 __device__ __forceinline__ bool project_rn(const float *P, float px, float py, float pz,
                                            int h, int w, float &xr, float &yr) {
+    // depth first: a voxel behind the camera (or at depth 0: inf / NaN lanes) is invalid whatever
+    // its pixel is (:154), so the two dot products and divisions are skipped for it
+    const float p2 = dot4_rn(P + 8, px, py, pz);
+    xr = yr = 0.f;
+    if (!(p2 > 0.0f)) return false;
     const float p0 = dot4_rn(P, px, py, pz);
     const float p1 = dot4_rn(P + 4, px, py, pz);
-    const float p2 = dot4_rn(P + 8, px, py, pz);
     xr = rintf(__fdiv_rn(p0, p2));
     yr = rintf(__fdiv_rn(p1, p2));
     // -0.0f >= 0 holds (pixel 0); NaN / inf compare false, like the reference's
     // cast-then-compare on every platform.
-    return (xr >= 0.0f) & (yr >= 0.0f) & (xr < (float)w) & (yr < (float)h) & (p2 > 0.0f);
+    return (xr >= 0.0f) & (yr >= 0.0f) & (xr < (float)w) & (yr < (float)h);
 }
 
 __device__ __forceinline__ void voxel_coords(const BpArgs &a, int b, int n, float &px,
@@ -241,7 +245,7 @@ __device__ __forceinline__ void finish_voxel(const BpArgs &a, OutT *vol, int n, 
 }
 
 template <int G, int CPL, int MODE, typename OutT>
-__global__ void __launch_bounds__(256) bp_vec_kernel(const __grid_constant__ BpArgs a) {
+__global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const __grid_constant__ BpArgs a) {
     extern __shared__ int smem[];
     constexpr unsigned FULL = 0xffffffffu;
     constexpr int VPI = 32 / G;                // voxels a warp works on at once
