@@ -836,6 +836,134 @@ extern "C" int ivx_backproject_scenes_nchw(const float *feat, const int64_t *fea
 }
 
 // ---------------------------------------------------------------------------
+// View-sharded finalize fused with its collective (multi-GPU).
+//
+// Every rank has written the fp32 partial sums / int32 counts of ITS views into
+// a buffer that all ranks of the NVLink domain can address (symmetric memory:
+// the same offset on every GPU).  Instead of an NCCL all-reduce followed by a
+// separate finalize pass, one kernel reads the partials of all ranks and
+// divides: through the NVSwitch multicast address with multimem.ld_reduce (the
+// switch adds the G copies and returns one value: NVLS) when the buffer has
+// one, else by loading each peer's copy over NVLink in rank order.  The result
+// is the same on every rank (same summation order everywhere).
+// ---------------------------------------------------------------------------
+namespace ivx {
+
+constexpr int kMaxPeers = 16;
+
+struct PeerArgs {
+    const float4 *sum[kMaxPeers];
+    const int32_t *count[kMaxPeers];
+    const float4 *mc_sum;      // multicast alias of the sum buffers, or nullptr
+    const int32_t *mc_count;   // multicast alias of the count buffers, or nullptr
+    int world;
+};
+
+__device__ __forceinline__ float4 multimem_sum_f32x4(const float4 *p) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "l"(p)
+                 : "memory");
+    return v;
+}
+
+__device__ __forceinline__ int multimem_sum_s32(const int32_t *p) {
+    int v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__global__ void __launch_bounds__(256) finalize_mean_peers_kernel(
+    const __grid_constant__ PeerArgs pa, long long n_rows, int c4, int N, void *vol, long long os_b,
+    long long os_c, long long os_n, int dtype, uint8_t *__restrict__ valid, int32_t *__restrict__ count_out) {
+    const long long total = n_rows * c4;
+    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / c4;
+        const int q = (int)(i - row * c4);
+        int cnt = 0;
+        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (pa.mc_sum != nullptr) {
+            s = multimem_sum_f32x4(pa.mc_sum + i);
+            cnt = multimem_sum_s32(pa.mc_count + row);
+        } else {
+            for (int r = 0; r < pa.world; ++r) {   // rank order: the same sum on every rank
+                const float4 t = __ldcs(pa.sum[r] + i);
+                s.x += t.x, s.y += t.y, s.z += t.z, s.w += t.w;
+                cnt += __ldg(pa.count[r] + row);
+            }
+        }
+        const float c = (float)cnt;
+        s.x = cnt ? __fdiv_rn(s.x, c) : 0.f;
+        s.y = cnt ? __fdiv_rn(s.y, c) : 0.f;
+        s.z = cnt ? __fdiv_rn(s.z, c) : 0.f;
+        s.w = cnt ? __fdiv_rn(s.w, c) : 0.f;
+        const long long b = row / N, n = row - b * N;
+        const long long base = b * os_b + n * os_n;
+        if (os_c == 1) {
+            if (dtype == IVX_F32)
+                store4<float>(reinterpret_cast<float *>(vol) + base + q * 4, s);
+            else
+                store4<__nv_bfloat16>(reinterpret_cast<__nv_bfloat16 *>(vol) + base + q * 4, s);
+        } else {
+            float *o = reinterpret_cast<float *>(vol) + base + (long long)q * 4 * os_c;
+            o[0] = s.x;
+            o[os_c] = s.y;
+            o[2 * os_c] = s.z;
+            o[3 * os_c] = s.w;
+        }
+        if (q == 0) {
+            if (valid) valid[row] = cnt > 0;
+            if (count_out) count_out[row] = cnt;
+        }
+    }
+}
+
+}  // namespace ivx
+
+extern "C" int ivx_finalize_mean_peers(const float *const *peer_sums, const int32_t *const *peer_counts,
+                                       int world, const float *mc_sum, const int32_t *mc_count,
+                                       int n_scenes, int n_channels, int64_t n_points, void *volume,
+                                       const int64_t *vol_strides, int vol_dtype, uint8_t *valid,
+                                       int32_t *count_out, void *stream) {
+    IVX_REQUIRE(volume && vol_strides, "NULL argument");
+    IVX_REQUIRE(world >= 1 && world <= kMaxPeers, "world size must be in [1, %d]", kMaxPeers);
+    IVX_REQUIRE((mc_sum != nullptr) == (mc_count != nullptr), "give both multicast pointers or neither");
+    IVX_REQUIRE(mc_sum != nullptr || (peer_sums != nullptr && peer_counts != nullptr),
+                "need the multicast pointers or the per-rank pointers");
+    IVX_REQUIRE(n_scenes > 0 && n_points > 0 && n_points < (1ll << 31), "sizes out of range");
+    IVX_REQUIRE(n_channels > 0 && n_channels % 4 == 0, "partial sums must be channels-last with C %% 4 == 0");
+    IVX_REQUIRE(vol_dtype == IVX_F32 || vol_dtype == IVX_BF16, "unknown vol_dtype %d", vol_dtype);
+    const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
+    if (vol_strides[1] == 1)
+        IVX_REQUIRE(vol_strides[0] % 4 == 0 && vol_strides[2] % 4 == 0 &&
+                        reinterpret_cast<uintptr_t>(volume) % (4 * esz) == 0,
+                    "channels-last volume must be aligned to 4 elements");
+    else
+        IVX_REQUIRE(vol_dtype == IVX_F32, "bf16 volumes must be channels-last");
+    PeerArgs pa;
+    pa.world = world;
+    pa.mc_sum = reinterpret_cast<const float4 *>(mc_sum);
+    pa.mc_count = mc_count;
+    for (int r = 0; r < kMaxPeers; ++r) {
+        pa.sum[r] = (peer_sums && r < world) ? reinterpret_cast<const float4 *>(peer_sums[r]) : nullptr;
+        pa.count[r] = (peer_counts && r < world) ? peer_counts[r] : nullptr;
+        if (mc_sum == nullptr && r < world)
+            IVX_REQUIRE(pa.sum[r] && pa.count[r] && aligned16(pa.sum[r]), "rank %d: bad partial pointers", r);
+    }
+    const long long rows = (long long)n_scenes * n_points;
+    const int c4 = n_channels / 4;
+    long long gx = (rows * c4 + 255) / 256;
+    if (gx > kNumSMs * 32) gx = kNumSMs * 32;
+    finalize_mean_peers_kernel<<<(unsigned)gx, 256, 0, (cudaStream_t)stream>>>(
+        pa, rows, c4, (int)n_points, volume, vol_strides[0], vol_strides[1], vol_strides[2], vol_dtype, valid,
+        count_out);
+    IVX_CHECK_LAUNCH("finalize_mean_peers launch");
+    return IVX_OK;
+}
+
+// ---------------------------------------------------------------------------
 // Allocation-free variant of ivx_backproject_scenes_nchw.
 //
 // Some users of this library run where device memory cannot be requested at

@@ -132,7 +132,7 @@ def backproject(features, points, projection):
 
 
 def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, *, points=None,
-                       out_dtype=torch.float32, channels_last=True, reduce="mean", repack=True):
+                       out_dtype=torch.float32, channels_last=True, reduce="mean", repack=True, out=None):
     """Fused back-projection + view reduction of a batch of scenes.
 
     Replaces the per-scene loop of ``extract_feat`` (:57-78): returns the
@@ -146,6 +146,8 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
                 if ``points`` ([3,X,Y,Z]) is given
     reduce      "mean" (the reference's result) or "partial" (fp32 sums and
                 counts for the view-sharded multi-GPU path)
+    out         optional pre-allocated ``(volume [B,N,C] dense, valid [B,N] bool, count [B,N]
+                int32)`` to write into (e.g. peer-addressable symmetric memory)
     repack      NCHW features with C % 4 == 0 are first re-laid to channels-last
                 in a scratch buffer (``ivx_backproject_scenes_nchw``); False
                 gathers from the strided maps directly
@@ -176,12 +178,18 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
         no = _lib.f32(flat)
     mode = {"mean": _lib.IVX_REDUCE_MEAN, "partial": _lib.IVX_REDUCE_PARTIAL}[reduce]
     dt = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}[out_dtype]
-    if channels_last:
+    if out is not None:
+        vol_nc, valid, count = out
+        if tuple(vol_nc.shape) != (b, n, c) or not vol_nc.is_contiguous() or vol_nc.dtype != out_dtype:
+            raise ValueError("out[0] must be a dense [B, N, C] tensor of the output dtype")
+        volume = vol_nc.permute(0, 2, 1)
+    elif channels_last:
         volume = torch.empty((b, n, c), dtype=out_dtype, device=dev).permute(0, 2, 1)
     else:
         volume = torch.empty((b, c, n), dtype=out_dtype, device=dev)
-    valid = torch.empty((b, n), dtype=torch.bool, device=dev)
-    count = torch.empty((b, n), dtype=torch.int32, device=dev)
+    if out is None:
+        valid = torch.empty((b, n), dtype=torch.bool, device=dev)
+        count = torch.empty((b, n), dtype=torch.int32, device=dev)
     args = (b, v, c, hw_arr, proj.data_ptr(), pp, g, no, n, volume.data_ptr(),
             _lib.i64(volume.stride()), dt, mode, valid.data_ptr(), count.data_ptr())
     with torch.cuda.device(dev):

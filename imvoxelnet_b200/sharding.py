@@ -15,7 +15,8 @@ one process per GPU, ``torch.distributed`` for the plumbing:
 import torch
 import torch.distributed as dist
 
-__all__ = ["shard_views", "shard_scenes", "allreduce_partials", "backproject_scenes_view_sharded"]
+__all__ = ["shard_views", "shard_scenes", "allreduce_partials", "backproject_scenes_view_sharded",
+           "FusedViewSharded"]
 
 
 def shard_views(n_views, rank, world_size):
@@ -68,3 +69,68 @@ def backproject_scenes_view_sharded(features, hw, projection, n_voxels, voxel_si
     allreduce_partials(s, cnt, group)
     volume, valid = ops.finalize_mean(s, cnt, out_dtype=out_dtype, channels_last=channels_last)
     return volume, valid, cnt
+
+
+class FusedViewSharded:
+    """View-sharded back-projection whose reduction is fused into the finalize kernel.
+
+    The partial sums and counts of every rank live in torch symmetric memory
+    (same offset on every GPU of the NVLink domain).  A step is: the fused
+    back-projection kernel writes this rank's partials there; a barrier over
+    the ranks; ``ivx_finalize_mean_peers`` reads all ranks' partials in place --
+    through the NVSwitch multicast address with ``multimem.ld_reduce`` when the
+    allocation has one (the switch does the sum), else peer by peer over NVLink
+    -- and divides; a second barrier frees the buffers for the next step.  No
+    NCCL call, no reduced copy of the partials in HBM.
+    """
+
+    def __init__(self, n_scenes, n_channels, n_voxels, group=None, device=None, use_multicast=True):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.device = torch.device(device if device is not None else torch.cuda.current_device())
+        self.shape = (int(n_scenes), int(n_channels), tuple(int(v) for v in n_voxels))
+        n = self.shape[2][0] * self.shape[2][1] * self.shape[2][2]
+        self.n_points = n
+        self.sum = symm_mem.empty((n_scenes, n, n_channels), dtype=torch.float32, device=self.device)
+        self.count = symm_mem.empty((n_scenes, n), dtype=torch.int32, device=self.device)
+        self._hs = symm_mem.rendezvous(self.sum, self.group)
+        self._hc = symm_mem.rendezvous(self.count, self.group)
+        self.world = self._hs.world_size
+        self.rank = self._hs.rank
+        self.multicast = bool(use_multicast and self._hs.multicast_ptr and self._hc.multicast_ptr)
+        self._valid = torch.empty((n_scenes, n), dtype=torch.bool, device=self.device)
+
+    def __call__(self, features, hw, projection, voxel_size, origins, *, out_dtype=torch.float32):
+        """``features`` / ``projection`` hold this rank's views (``shard_views``); a rank
+        without views passes ``V_local == 0`` tensors.  Returns ``(volume, valid, count)``,
+        identical on every rank."""
+        import ctypes
+
+        from . import _lib, ops
+        b, c, nv = self.shape
+        n = self.n_points
+        if features.shape[1] > 0:
+            ops.backproject_scenes(features, hw, projection, nv, voxel_size, origins, reduce="partial",
+                                   out=(self.sum, self._valid, self.count))
+        else:
+            self.sum.zero_()
+            self.count.zero_()
+        self._hs.barrier(channel=0)          # every rank's partials are written and visible
+        volume = torch.empty((b, n, c), dtype=out_dtype, device=self.device).permute(0, 2, 1)
+        valid = torch.empty((b, n), dtype=torch.bool, device=self.device)
+        count = torch.empty((b, n), dtype=torch.int32, device=self.device)
+        if self.multicast:
+            sums = counts = None
+            mc_sum, mc_count = self._hs.multicast_ptr, self._hc.multicast_ptr
+        else:
+            sums = (ctypes.c_void_p * self.world)(*[int(p) for p in self._hs.buffer_ptrs])
+            counts = (ctypes.c_void_p * self.world)(*[int(p) for p in self._hc.buffer_ptrs])
+            mc_sum = mc_count = None
+        dt = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}[out_dtype]
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.lib().ivx_finalize_mean_peers(
+                sums, counts, self.world, mc_sum, mc_count, b, c, n, volume.data_ptr(),
+                _lib.i64(volume.stride()), dt, valid.data_ptr(), count.data_ptr(),
+                torch.cuda.current_stream().cuda_stream), "ivx_finalize_mean_peers")
+        self._hs.barrier(channel=1)          # nobody overwrites partials that a peer still reads
+        return (volume.unflatten(2, nv), valid.view((b, 1) + nv), count.view((b,) + nv))

@@ -157,6 +157,26 @@ IVX_API int ivx_finalize_mean(const float *sum, const int32_t *count, int n_scen
                       uint8_t *valid, void *stream);
 
 /*
+ * ivx_finalize_mean_peers -- ivx_finalize_mean fused with its collective: the
+ * partial sums / counts of all `world` ranks are read in place, either through
+ * the NVSwitch multicast alias of the buffers (mc_sum / mc_count non-NULL:
+ * multimem.ld_reduce, the switch does the addition) or from each rank's copy
+ * over NVLink (peer_sums / peer_counts: host arrays of `world` device
+ * pointers, summed in rank order), then divided and masked
+ * (detectors/imvoxelnet.py:70-74).  The buffers must be peer-addressable
+ * (e.g. torch symmetric memory) and every rank must have finished -- and made
+ * visible -- its partial kernel before any rank calls this (a barrier over the
+ * ranks on the stream); layout as for ivx_finalize_mean.  The reference has
+ * no multi-GPU form of this path at all.
+ */
+IVX_API int ivx_finalize_mean_peers(const float *const *peer_sums /* host[world] */,
+                                    const int32_t *const *peer_counts /* host[world] */, int world,
+                                    const float *mc_sum, const int32_t *mc_count, int n_scenes,
+                                    int n_channels, int64_t n_points, void *volume,
+                                    const int64_t *vol_strides /* host[3] */, int vol_dtype,
+                                    uint8_t *valid, int32_t *count_out, void *stream);
+
+/*
  * ivx_repack_nchw_to_nhwc -- layout pass for callers that hold the reference's
  * NCHW maps: dst[i][y][x][c] = src[i][c][y][x] for i < n_images (tiled through
  * shared memory, coalesced on both sides).  src_strides: host, 4 element

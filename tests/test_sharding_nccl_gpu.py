@@ -42,7 +42,21 @@ def _worker(rank, world, port, out):
         vol, valid, cnt = sharding.backproject_scenes_view_sharded(
             feats, [(h, w)] * 2, P[:, mine].contiguous(), sc.n_voxels, sc.voxel_size, [origin] * 2)
         torch.cuda.synchronize()
-        np.savez(out % rank, vol=vol.cpu().numpy(), valid=valid.cpu().numpy(), cnt=cnt.cpu().numpy())
+        blob = dict(vol=vol.cpu().numpy(), valid=valid.cpu().numpy(), cnt=cnt.cpu().numpy())
+        # the same step with the reduction fused into the finalize kernel (peer loads, then multicast)
+        for name, use_mc in (("peer", False), ("mc", True)):
+            try:
+                fused = sharding.FusedViewSharded(2, sc.channels, sc.n_voxels, use_multicast=use_mc)
+            except Exception as exc:   # symmetric memory may be unavailable in a sandbox
+                blob[f"{name}_error"] = np.array(str(exc)[:200])
+                continue
+            for _ in range(2):         # twice: the buffers are reused
+                v2, ok2, c2 = fused(feats, [(h, w)] * 2, P[:, mine].contiguous(), sc.voxel_size, [origin] * 2)
+            torch.cuda.synchronize()
+            blob[f"{name}_vol"], blob[f"{name}_valid"], blob[f"{name}_cnt"] = \
+                v2.cpu().numpy(), ok2.cpu().numpy(), c2.cpu().numpy()
+            blob[f"{name}_multicast"] = np.array(fused.multicast)
+        np.savez(out % rank, **blob)
     finally:
         dist.destroy_process_group()
 
@@ -60,3 +74,15 @@ def test_view_sharded_equals_single_gpu(tmp_path):
         assert np.array_equal(got["valid"], ref[1].cpu().numpy())
         assert np.array_equal(got["cnt"], ref[2].cpu().numpy())
         assert_volume_close(got["vol"], ref[0].cpu().numpy())
+        for name in ("peer", "mc"):
+            if f"{name}_error" in got.files:
+                print(f"fused path ({name}) unavailable here:", got[f"{name}_error"])
+                continue
+            print(f"fused path ({name}): multicast used =", bool(got[f"{name}_multicast"]))
+            assert np.array_equal(got[f"{name}_valid"], ref[1].cpu().numpy())
+            assert np.array_equal(got[f"{name}_cnt"], ref[2].cpu().numpy())
+            assert_volume_close(got[f"{name}_vol"], ref[0].cpu().numpy())
+    a, b = np.load(out % 0), np.load(out % 1)
+    for name in ("peer", "mc"):                       # replicated result: bit-identical on both ranks
+        if f"{name}_vol" in a.files and f"{name}_vol" in b.files:
+            assert np.array_equal(a[f"{name}_vol"], b[f"{name}_vol"])
