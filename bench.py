@@ -293,7 +293,19 @@ def run_ours(args):
     hws = [(h, w)] * batch
     origins = [origin] * batch
 
+    fused = None
+    if view_sharded and args.collective != "nccl":
+        try:
+            # two ranks: one peer copy to read, plain NVLink loads win; more ranks: let the switch add
+            use_mc = args.collective == "multimem" or (args.collective == "auto" and world > 2)
+            fused = sharding.FusedViewSharded(batch, C, sc.n_voxels, use_multicast=use_mc)
+        except Exception as exc:
+            if rank == 0:
+                print(f"[bench] symmetric memory unavailable ({exc}); using the NCCL all-reduce", file=sys.stderr)
+
     def backproject(feats, proj, out_dtype):
+        if fused is not None:
+            return fused(feats, hws, proj, sc.voxel_size, origins, out_dtype=out_dtype)
         if view_sharded:
             return sharding.backproject_scenes_view_sharded(feats, hws, proj, sc.n_voxels, sc.voxel_size,
                                                             origins, out_dtype=out_dtype)
@@ -476,7 +488,12 @@ def run_ours(args):
             "data": "synthetic",
             "config": config_of(sc, batch, world, {
                 "stages": stage_names,
-                "parallelism": (f"views sharded over {world} ranks + NCCL all-reduce" if view_sharded
+                "parallelism": (f"views sharded over {world} ranks + " +
+                                ("NCCL all-reduce" if fused is None else
+                                 "reduction fused into the finalize kernel (" +
+                                 ("multimem.ld_reduce over the NVSwitch multicast address"
+                                  if fused.multicast else "peer loads over NVLink") + ")")
+                                if view_sharded
                                 else f"scenes data-parallel x{world}, no collective"),
                 "l2": f"{n_sets} rotating input sets; activations written per step >> 126 MB L2",
                 "layout": "features NHWC fp32, volume and neck activations NDHWC"}),
@@ -525,6 +542,8 @@ def main():
     ap.add_argument("--neck-precision", default="bf16", choices=["bf16", "fp32"],
                     help="bf16: tcgen05 kernels (1e-2 of the reference); fp32: CUDA-core parity path (1e-5)")
     ap.add_argument("--no-neck", action="store_true", help="time the back-projection stage only")
+    ap.add_argument("--collective", default="auto", choices=["auto", "multimem", "peer", "nccl"],
+                    help="view-sharded mode (scannet_fast, N > 1): how the partial sums are reduced")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3
