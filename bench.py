@@ -40,6 +40,7 @@ WORKLOADS = {
     "scannet_fast": ("scannet_fast", 8),
     "sunrgbd_fast": ("sunrgbd_fast", 8),
     "nuscenes": ("nuscenes", 8),
+    "nuscenes_refgrid": ("nuscenes_refgrid", 4),   # the reference's own 312x312x12 grid (neck-compatible)
     "total_sunrgbd": ("total_sunrgbd", 32),
 }
 METRIC = "voxel_views_per_s"   # through the whole hot path: back-projection + 3D neck
@@ -127,6 +128,7 @@ NECKS = {
     "total_sunrgbd": ("ImVoxelNeck", dict(channels=[64, 128, 256, 512], out_channels=64,
                                           down_layers=[1, 2, 3, 4], up_layers=[3, 2, 1], conditional=False), 631.66),
     "nuscenes": None,   # BASELINE's 200x200x4 grid: every reference neck rejects Z=4
+    "nuscenes_refgrid": ("NuScenesImVoxelNeck", dict(in_channels=64, out_channels=256), 1571.76),
 }
 
 
@@ -418,7 +420,8 @@ def run_ours(args):
             # dominant kernel of the step: conv3d_tc_kernel (tcgen05 implicit GEMM), timed inside a long step
             roofline = {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
                         "frac": tflops / peak, "frac_of_burst_peak": tflops / peaks["bf16_tflops"],
-                        "traffic": None, "kernel": "conv3d_tc_halo_kernel / conv3d_tc_kernel", "peak_kind": peak_kind + " (sustained)",
+                        "traffic": _ncu_traffic("neck_" + sc.name),
+                        "kernel": "conv3d_tc_halo_kernel / conv3d_tc_kernel", "peak_kind": peak_kind + " (sustained)",
                         "algorithmic_flops_per_step": neck_gflop * batch * 1e9,
                         "launches_per_step": launches // max(args.steps, 1) - 1}
 

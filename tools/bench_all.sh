@@ -1,6 +1,6 @@
 #!/bin/bash
 # Run bench.py on every workload and print a one-line digest of each (GPU box).
-for w in kitti scannet_fast sunrgbd_fast nuscenes total_sunrgbd; do
+for w in kitti scannet_fast sunrgbd_fast nuscenes nuscenes_refgrid total_sunrgbd; do
   python bench.py --workload $w "$@" > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err || { echo "$w FAILED"; tail -5 gpurun_out/bench_$w.err; continue; }
   python - <<PY
 import json
