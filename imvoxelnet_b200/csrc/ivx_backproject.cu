@@ -372,6 +372,74 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
 }
 
 // ---------------------------------------------------------------------------
+// Backward of the fused back-projection + view mean with respect to the
+// features (what autograd does through :157 and :70-74 in the reference):
+//   grad_feat[b, v, :, y, x] += grad_volume[b, :, n] / count[b, n]   for every hit (v, n)
+// Same tiling and hit lists as the forward kernel; several voxels may hit one
+// pixel, so the scatter uses 128-bit vector reductions (red.global.add.v4.f32).
+// ---------------------------------------------------------------------------
+template <int G, int CPL>
+__global__ void __launch_bounds__(256, 4) bp_backward_kernel(const __grid_constant__ BpArgs a) {
+    extern __shared__ int smem[];
+    constexpr unsigned FULL = 0xffffffffu;
+    constexpr int VPI = 32 / G;
+    const int b = blockIdx.y;
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    const int T = 1 << a.tile_log2;
+
+    float *sP = reinterpret_cast<float *>(smem);
+    for (int i = threadIdx.x; i < a.V * 12; i += blockDim.x)
+        sP[i] = __ldg(a.proj + b * a.proj_stride_b + i);
+    __syncthreads();
+    int *table = smem + ((a.V * 12 + 3) & ~3) + warp * T * a.table_stride;
+
+    // here a.feat is the GRADIENT of the features (written), a.vol the gradient of the volume (read)
+    float4 *gfeat4 = reinterpret_cast<float4 *>(const_cast<float *>(a.feat) + b * a.fs_b);
+    const float *gvol = reinterpret_cast<const float *>(a.vol) + b * a.os_b;
+    const int g = lane / G;
+    const int t = lane % G;
+    const int ntiles = (a.N + T - 1) >> a.tile_log2;
+
+    for (int tile = blockIdx.x * nwarps + warp; tile < ntiles; tile += gridDim.x * nwarps) {
+        const int n0 = tile << a.tile_log2;
+        const int my_cnt = fill_table<true>(a, sP, table, b, n0, lane);
+        for (int j0 = 0; j0 < T; j0 += VPI) {
+            const int j = j0 + g;
+            const int n = n0 + j;
+            int cnt = __shfl_sync(FULL, my_cnt, j & 31);
+            if (j >= T || n >= a.N) cnt = 0;
+            if (cnt == 0) continue;
+            const int *row = table + j * a.table_stride;
+            const float c = (float)cnt;
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) {
+                if ((t + i * G) * 4 >= a.C) continue;
+                float4 gv = __ldcs(reinterpret_cast<const float4 *>(gvol + (long long)n * a.os_n) + t + i * G);
+                if (a.reduce == IVX_REDUCE_MEAN) {
+                    gv.x = __fdiv_rn(gv.x, c), gv.y = __fdiv_rn(gv.y, c);
+                    gv.z = __fdiv_rn(gv.z, c), gv.w = __fdiv_rn(gv.w, c);
+                }
+                for (int k = 0; k < cnt; ++k) atomicAdd(gfeat4 + row[k] + t + i * G, gv);
+            }
+        }
+        __syncwarp();
+    }
+}
+
+static void *pick_backward_kernel(int C) {
+    const int c4 = (C + 3) / 4;
+    if (c4 <= 8) return (void *)bp_backward_kernel<8, 1>;
+    if (c4 <= 16) return (void *)bp_backward_kernel<16, 1>;
+    if (c4 <= 32) return (void *)bp_backward_kernel<32, 1>;
+    if (c4 <= 64) return (void *)bp_backward_kernel<32, 2>;
+    if (c4 <= 128) return (void *)bp_backward_kernel<32, 4>;
+    if (c4 <= 256) return (void *)bp_backward_kernel<32, 8>;
+    return nullptr;
+}
+
+// ---------------------------------------------------------------------------
 // Strided kernel: any feature strides (the reference's NCHW slice, :69), any
 // channel count, any fp32 volume strides.  Lanes own channels.
 // ---------------------------------------------------------------------------
@@ -564,14 +632,18 @@ static void *pick_vec_kernel(int C, int V) {
 static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // One launch over at most IVX_MAX_SCENES_PER_LAUNCH scenes.
-static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t stream) {
+static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t stream, bool backward = false) {
     const bool feat_vec = a.fs_c == 1 && a.C % 4 == 0 && aligned16(a.feat) && a.fs_b % 4 == 0 &&
                           a.fs_v % 4 == 0 && a.fs_h % 4 == 0 && a.fs_w % 4 == 0;
     const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
     const bool vol_vec = a.os_c == 1 && a.os_b % 4 == 0 && a.os_n % 4 == 0 &&
                          (reinterpret_cast<uintptr_t>(a.vol) % (4 * esz)) == 0;
     void *kernel = nullptr;
-    if (feat_vec && vol_vec)
+    if (backward) {
+        if (!(feat_vec && vol_vec) || vol_dtype != IVX_F32 || (kernel = pick_backward_kernel(a.C)) == nullptr)
+            return fail(IVX_ERR_UNSUPPORTED,
+                        "backward needs channels-last fp32 gradients with C %% 4 == 0 and C <= 1024");
+    } else if (feat_vec && vol_vec)
         kernel = vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16>(a.C, a.V)
                                         : pick_vec_kernel<float>(a.C, a.V);
     if (kernel != nullptr) {
@@ -647,7 +719,7 @@ static int backproject_batch(const float *feat, const long long fs[5], int B, in
                              long long proj_stride_b, const float *points, const ivx_grid *grid,
                              const float *new_origin, bool origin_per_scene, int64_t N, void *volume,
                              const int64_t *vs, int vol_dtype, int reduce, uint8_t *valid,
-                             int32_t *count, cudaStream_t stream) {
+                             int32_t *count, cudaStream_t stream, bool backward = false) {
     const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
     for (int b0 = 0; b0 < B; b0 += IVX_MAX_SCENES_PER_LAUNCH) {
         const int nb = (B - b0 < IVX_MAX_SCENES_PER_LAUNCH) ? B - b0 : IVX_MAX_SCENES_PER_LAUNCH;
@@ -679,7 +751,7 @@ static int backproject_batch(const float *feat, const long long fs[5], int B, in
                 a.new_origin[b][k] =
                     new_origin ? new_origin[(origin_per_scene ? 3 * (b0 + b) : 0) + k] : 0.f;
         }
-        int rc = launch_scenes(a, nb, vol_dtype, stream);
+        int rc = launch_scenes(a, nb, vol_dtype, stream, backward);
         if (rc != IVX_OK) return rc;
     }
     return IVX_OK;
@@ -733,6 +805,28 @@ extern "C" int ivx_backproject_scenes(const float *feat, const int64_t *feat_str
     return backproject_batch(feat, fs, n_scenes, n_views, n_channels, hw, true, proj,
                              12ll * n_views, points, grid, new_origin, true, n_points, volume,
                              vol_strides, vol_dtype, reduce, valid, count, (cudaStream_t)stream);
+}
+
+extern "C" int ivx_backproject_scenes_backward(const float *grad_volume, const int64_t *gvol_strides,
+                                               float *grad_feat, const int64_t *feat_strides, int n_scenes,
+                                               int n_views, int n_channels, const int32_t *hw,
+                                               const float *proj, const float *points, const ivx_grid *grid,
+                                               const float *new_origin, int64_t n_points, int reduce,
+                                               void *stream) {
+    int rc = validate_grid(points, grid, new_origin, n_points);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(grad_volume && gvol_strides && grad_feat && feat_strides && hw && proj, "NULL argument");
+    IVX_REQUIRE(n_scenes > 0 && n_channels > 0, "n_scenes and n_channels must be positive");
+    IVX_REQUIRE(n_views > 0 && n_views <= IVX_MAX_VIEWS, "n_views must be in [1, %d]", IVX_MAX_VIEWS);
+    IVX_REQUIRE(reduce == IVX_REDUCE_MEAN || reduce == IVX_REDUCE_PARTIAL, "unknown reduce %d", reduce);
+    for (int b = 0; b < n_scenes; ++b)
+        IVX_REQUIRE(hw[2 * b] > 0 && hw[2 * b + 1] > 0, "scene %d: height/width must be positive", b);
+    const long long fs[5] = {feat_strides[0], feat_strides[1], feat_strides[2], feat_strides[3],
+                             feat_strides[4]};
+    // the forward machinery with the roles of the buffers exchanged: the "features" are written
+    return backproject_batch(grad_feat, fs, n_scenes, n_views, n_channels, hw, true, proj, 12ll * n_views,
+                             points, grid, new_origin, true, n_points, const_cast<float *>(grad_volume),
+                             gvol_strides, IVX_F32, reduce, nullptr, nullptr, (cudaStream_t)stream, true);
 }
 
 extern "C" int ivx_backproject_views(const float *feat, const int64_t *feat_strides, int n_views,

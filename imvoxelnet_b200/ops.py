@@ -49,8 +49,30 @@ def _need_cuda(t, name):
 def _no_grad(features):
     if torch.is_grad_enabled() and features.requires_grad:
         raise NotImplementedError(
-            "backproject: autograd through the fused kernel (SURVEY.md section 8(f)-1) is not "
-            "implemented yet; call under torch.no_grad()")
+            "this entry point has no autograd support; backproject_scenes(reduce='mean' or 'partial', "
+            "fp32, channels-last) is differentiable with respect to the features")
+
+
+class _BackprojectScenes(torch.autograd.Function):
+    """Differentiable (w.r.t. the features) fused back-projection: forward
+    ``ivx_backproject_scenes``, backward ``ivx_backproject_scenes_backward``."""
+
+    @staticmethod
+    def forward(ctx, features, call):
+        volume, valid, count = call(features.detach())
+        ctx.call_backward = call.backward
+        ctx.feat_meta = (features.shape, features.stride())
+        ctx.mark_non_differentiable(valid, count)
+        return volume, valid, count
+
+    @staticmethod
+    def backward(ctx, grad_volume, _gv, _gc):
+        shape, stride = ctx.feat_meta
+        grad_feat = torch.zeros(shape, dtype=torch.float32, device=grad_volume.device)
+        if stride[2] == 1:      # same channels-last layout as the features
+            grad_feat = grad_feat.permute(0, 1, 3, 4, 2).contiguous().permute(0, 1, 4, 2, 3)
+        ctx.call_backward(grad_volume, grad_feat)
+        return grad_feat, None
 
 
 def _proj_dev(projection, device):
@@ -154,7 +176,25 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
     """
     global _launches
     _need_cuda(features, "features")
-    _no_grad(features)
+    if torch.is_grad_enabled() and features.requires_grad:
+        # training: the same kernels under autograd (gradient w.r.t. the features only, as upstream:
+        # get_points is @no_grad and the projection comes from the metadata)
+        if out is not None or out_dtype != torch.float32 or not channels_last or features.shape[2] % 4:
+            raise NotImplementedError("autograd needs fp32, channels-last volumes and C % 4 == 0")
+        kw = dict(points=points, out_dtype=out_dtype, channels_last=True, reduce=reduce, repack=repack)
+        feats_cl = features if features.stride(2) == 1 else \
+            features.permute(0, 1, 3, 4, 2).contiguous().permute(0, 1, 4, 2, 3)
+
+        def call(f):
+            with torch.no_grad():
+                return backproject_scenes(f, hw, projection, n_voxels, voxel_size, origins, **kw)
+
+        def call_backward(grad_volume, grad_feat):
+            _backproject_scenes_backward(grad_volume, grad_feat, hw, projection, n_voxels, voxel_size,
+                                         origins, points, reduce)
+
+        call.backward = call_backward
+        return _BackprojectScenes.apply(feats_cl, call)
     if features.dtype != torch.float32 or features.dim() != 5:
         raise TypeError("features must be a float32 [B,V,C,Hf,Wf] tensor")
     b, v, c = features.shape[:3]
@@ -208,6 +248,36 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
     _launches += (b + 63) // 64
     return (volume.unflatten(2, (xs, ys, zs)), valid.view(b, 1, xs, ys, zs),
             count.view(b, xs, ys, zs))
+
+
+def _backproject_scenes_backward(grad_volume, grad_feat, hw, projection, n_voxels, voxel_size, origins,
+                                 points, reduce):
+    """grad_feat (zero-filled, channels-last [B,V,C,Hf,Wf]) += scatter of grad_volume [B,C,X,Y,Z]."""
+    global _launches
+    b, v, c = grad_feat.shape[:3]
+    dev = grad_feat.device
+    xs, ys, zs = (int(t) for t in n_voxels)
+    n = xs * ys * zs
+    gv = grad_volume.reshape(b, c, n)
+    if gv.stride(1) != 1 or gv.stride(2) != c or gv.dtype != torch.float32:
+        gv = gv.float().permute(0, 2, 1).contiguous().permute(0, 2, 1)      # NDHWC, dense
+    proj = _proj_dev(projection, dev).reshape(b, v, 12)
+    hw_arr = _lib.i32([int(t) for pair in hw for t in pair])
+    if points is not None:
+        pts = _points_arg(points, dev)
+        pp, g, no = pts.data_ptr(), None, None
+    else:
+        pp, g = None, _lib.grid(n_voxels, voxel_size)
+        flat = []
+        for o in origins:
+            flat += _new_origin(n_voxels, voxel_size, o)
+        no = _lib.f32(flat)
+    mode = {"mean": _lib.IVX_REDUCE_MEAN, "partial": _lib.IVX_REDUCE_PARTIAL}[reduce]
+    with torch.cuda.device(dev):
+        _lib.check(_lib.lib().ivx_backproject_scenes_backward(
+            gv.data_ptr(), _lib.i64(gv.stride()), grad_feat.data_ptr(), _lib.i64(grad_feat.stride()), b, v, c,
+            hw_arr, proj.data_ptr(), pp, g, no, n, mode, _stream()), "ivx_backproject_scenes_backward")
+    _launches += (b + 63) // 64
 
 
 def finalize_mean(partial_sum, count, *, out_dtype=torch.float32, channels_last=True):

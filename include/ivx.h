@@ -131,6 +131,25 @@ IVX_API int ivx_backproject_scenes(const float *feat, const int64_t *feat_stride
                            void *stream);
 
 /*
+ * ivx_backproject_scenes_backward -- gradient of ivx_backproject_scenes with
+ * respect to the features: what autograd computes in the reference through
+ * the masked gather of detectors/imvoxelnet.py:157 and the view mean of
+ * :70-74 (training, forward_train :82-87).  For every hit (view v, voxel n):
+ *   grad_feat[b, v, :, y, x] += grad_volume[b, :, n] / count[b, n]
+ * (IVX_REDUCE_PARTIAL: no division).  grad_feat must be zero-filled by the
+ * caller; it and grad_volume are fp32, channels-last (stride_c == 1,
+ * C % 4 == 0), addressed like feat / volume of the forward call.  Duplicated
+ * pixels are accumulated with atomic vector adds (summation order not fixed).
+ */
+IVX_API int ivx_backproject_scenes_backward(const float *grad_volume,
+                                            const int64_t *gvol_strides /* host[3] */, float *grad_feat,
+                                            const int64_t *feat_strides /* host[5] */, int n_scenes,
+                                            int n_views, int n_channels, const int32_t *hw /* host[B][2] */,
+                                            const float *proj, const float *points, const ivx_grid *grid,
+                                            const float *new_origin /* host[B][3] */, int64_t n_points,
+                                            int reduce, void *stream);
+
+/*
  * ivx_backproject_views -- strict drop-in for the reference function
  * backproject(features, points, projection) (detectors/imvoxelnet.py:145-160):
  * per-view volumes [V][C][N] fp32 (zeros where invalid) and valid [V][N].

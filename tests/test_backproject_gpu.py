@@ -347,3 +347,37 @@ def test_streamed_hot_path_equals_serial_calls():
         assert torch.equal(outs[0], ref_outs[0].cpu()) and torch.equal(valid, ref_valid.cpu())
         n += 1
     assert n == 5
+
+
+@pytest.mark.parametrize("name,channels", [("scannet_fast", 32), ("kitti", 64), ("nuscenes", 16)])
+def test_gradient_wrt_features_matches_autograd_of_the_reference_ops(name, channels):
+    """Training support (back-projection part): d(loss)/d(features)
+    through the fused kernels == torch autograd through the reference's op sequence."""
+    from oracle import torch_port
+    sc = scenes.build(name)
+    if name != "nuscenes":
+        sc.n_voxels = tuple(max(4, v // 4) for v in sc.n_voxels)
+        sc.voxel_size = tuple(v * 4 for v in sc.voxel_size)
+    sc.channels = channels
+    origin = sc.img_meta['lidar2img']['origin']
+    P = pj.compute_projection(sc.img_meta, scenes.STRIDE)
+    h, w = sc.feat_hw
+    full = scenes.random_features(sc, seed=77, channels_last=True)
+    g = torch.Generator().manual_seed(5)
+    weight = torch.randn((channels,) + tuple(sc.n_voxels), generator=g)
+
+    feats = full.to(DEV)[None].requires_grad_(True)
+    vol, valid, cnt = ops.backproject_scenes(feats, [(h, w)], P[None], sc.n_voxels, sc.voxel_size, [origin])
+    assert vol.requires_grad and not valid.requires_grad
+    (vol[0] * weight.to(DEV)).sum().backward()
+    got = feats.grad[0].cpu()
+
+    ref_in = full.clone().contiguous().requires_grad_(True)
+    pts = pj.get_points(sc.n_voxels, sc.voxel_size, origin)
+    ref_vol, _ = torch_port.scene_volume(ref_in[:, :, :h, :w], pts, P)
+    (ref_vol * weight).sum().backward()
+    want = ref_in.grad
+    assert got.shape == want.shape
+    assert float(want.abs().max()) > 0
+    assert_volume_close(got.numpy(), want.numpy())
+    assert_volume_close(vol[0].detach().cpu().numpy(), ref_vol.detach().numpy())
