@@ -307,7 +307,8 @@ def run_ours(args):
 
     def backproject(feats, proj, out_dtype):
         if fused is not None:
-            return fused(feats, hws, proj, sc.voxel_size, origins, out_dtype=out_dtype)
+            # reduce-scatter semantics: this rank gets (and runs the neck on) its slice of the scenes
+            return fused(feats, hws, proj, sc.voxel_size, origins, out_dtype=out_dtype, scatter_scenes=True)
         if view_sharded:
             return sharding.backproject_scenes_view_sharded(feats, hws, proj, sc.n_voxels, sc.voxel_size,
                                                             origins, out_dtype=out_dtype)
@@ -495,7 +496,8 @@ def run_ours(args):
                                 ("NCCL all-reduce" if fused is None else
                                  "reduction fused into the finalize kernel (" +
                                  ("multimem.ld_reduce over the NVSwitch multicast address"
-                                  if fused.multicast else "peer loads over NVLink") + ")")
+                                  if fused.multicast else "peer loads over NVLink") +
+                                 "), scenes scattered: each rank runs the neck on its own scenes")
                                 if view_sharded
                                 else f"scenes data-parallel x{world}, no collective"),
                 "l2": f"{n_sets} rotating input sets; activations written per step >> 126 MB L2",

@@ -100,10 +100,13 @@ class FusedViewSharded:
         self.multicast = bool(use_multicast and self._hs.multicast_ptr and self._hc.multicast_ptr)
         self._valid = torch.empty((n_scenes, n), dtype=torch.bool, device=self.device)
 
-    def __call__(self, features, hw, projection, voxel_size, origins, *, out_dtype=torch.float32):
+    def __call__(self, features, hw, projection, voxel_size, origins, *, out_dtype=torch.float32,
+                 scatter_scenes=False):
         """``features`` / ``projection`` hold this rank's views (``shard_views``); a rank
-        without views passes ``V_local == 0`` tensors.  Returns ``(volume, valid, count)``,
-        identical on every rank."""
+        without views passes ``V_local == 0`` tensors.  Returns ``(volume, valid, count)``:
+        of all scenes, identical on every rank (all-reduce semantics), or with
+        ``scatter_scenes`` only of this rank's ``shard_scenes`` slice (reduce-scatter
+        semantics: every rank then runs the neck on its own scenes, none is replicated)."""
         import ctypes
 
         from . import _lib, ops
@@ -116,15 +119,21 @@ class FusedViewSharded:
             self.sum.zero_()
             self.count.zero_()
         self._hs.barrier(channel=0)          # every rank's partials are written and visible
+        mine = shard_scenes(b, self.rank, self.world) if scatter_scenes else slice(0, b)
+        b0, b = mine.start, mine.stop - mine.start
         volume = torch.empty((b, n, c), dtype=out_dtype, device=self.device).permute(0, 2, 1)
         valid = torch.empty((b, n), dtype=torch.bool, device=self.device)
         count = torch.empty((b, n), dtype=torch.int32, device=self.device)
+        off_s, off_c = b0 * n * c * 4, b0 * n * 4      # byte offsets of the first scene of the slice
+        if b == 0:
+            self._hs.barrier(channel=1)
+            return (volume.unflatten(2, nv), valid.view((0, 1) + nv), count.view((0,) + nv))
         if self.multicast:
             sums = counts = None
-            mc_sum, mc_count = self._hs.multicast_ptr, self._hc.multicast_ptr
+            mc_sum, mc_count = self._hs.multicast_ptr + off_s, self._hc.multicast_ptr + off_c
         else:
-            sums = (ctypes.c_void_p * self.world)(*[int(p) for p in self._hs.buffer_ptrs])
-            counts = (ctypes.c_void_p * self.world)(*[int(p) for p in self._hc.buffer_ptrs])
+            sums = (ctypes.c_void_p * self.world)(*[int(p) + off_s for p in self._hs.buffer_ptrs])
+            counts = (ctypes.c_void_p * self.world)(*[int(p) + off_c for p in self._hc.buffer_ptrs])
             mc_sum = mc_count = None
         dt = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}[out_dtype]
         with torch.cuda.device(self.device):

@@ -56,6 +56,10 @@ def _worker(rank, world, port, out):
             blob[f"{name}_vol"], blob[f"{name}_valid"], blob[f"{name}_cnt"] = \
                 v2.cpu().numpy(), ok2.cpu().numpy(), c2.cpu().numpy()
             blob[f"{name}_multicast"] = np.array(fused.multicast)
+            v3, ok3, c3 = fused(feats, [(h, w)] * 2, P[:, mine].contiguous(), sc.voxel_size, [origin] * 2,
+                                scatter_scenes=True)
+            torch.cuda.synchronize()
+            blob[f"{name}_slice_vol"], blob[f"{name}_slice_cnt"] = v3.cpu().numpy(), c3.cpu().numpy()
         np.savez(out % rank, **blob)
     finally:
         dist.destroy_process_group()
@@ -82,6 +86,10 @@ def test_view_sharded_equals_single_gpu(tmp_path):
             assert np.array_equal(got[f"{name}_valid"], ref[1].cpu().numpy())
             assert np.array_equal(got[f"{name}_cnt"], ref[2].cpu().numpy())
             assert_volume_close(got[f"{name}_vol"], ref[0].cpu().numpy())
+            # reduce-scatter flavour: rank r holds scene r of the two
+            assert got[f"{name}_slice_vol"].shape[0] == 1
+            assert np.array_equal(got[f"{name}_slice_cnt"][0], ref[2][rank].cpu().numpy())
+            assert_volume_close(got[f"{name}_slice_vol"][0], ref[0][rank].cpu().numpy())
     a, b = np.load(out % 0), np.load(out % 1)
     for name in ("peer", "mc"):                       # replicated result: bit-identical on both ranks
         if f"{name}_vol" in a.files and f"{name}_vol" in b.files:
