@@ -24,6 +24,12 @@
 // accumulator is therefore D^T (lane = channel, column = voxel): the epilogue has the
 // folded BN scale/shift as per-thread constants and transposes through shared memory.
 //
+// 64-channel layers would leave accumulator lanes 64..127 idle; instead they hold the NEXT
+// output plane (pack2): an input plane p feeds output plane r0 with tap dR = p - r0 + pad and
+// plane r0 + 1 with tap dR - 1, through the same shifted box, so the weight stage gets the two
+// 64-row slices (an out-of-range tap is fetched from beyond the weight tensor: the TMA
+// zero-fills it) and 4 input planes x 9 MMAs produce two output planes instead of 2 x 27.
+//
 // Warp roles (224 threads): 0 activation-plane producer, 1 MMA issuer, 2 weight
 // producer, 3..6 epilogue.
 #include "ivx_tc_ptx.cuh"
@@ -36,6 +42,7 @@ constexpr int HL_P = 8, HL_PPAD = 10, HL_QT = 16;  // outputs per group, box row
 struct HaloArgs {
     int c_in, c_out, n_tile, n_splits;
     int mt;                    // accumulator tiles per CTA along Q (1 or 2)
+    int pack2;                 // 64-channel tiles: lanes 64..127 hold the NEXT output plane (r0 + 1)
     int dims[3];               // output extent along P, Q, R (== input extent + 2*pad - 2)
     int pad[3];                // padding along P, Q, R
     int stride_r;              // conv stride along R (P and Q are stride 1)
@@ -65,7 +72,7 @@ __device__ __forceinline__ HaloTile decode_halo_tile(const HaloArgs &a, long lon
     t /= a.tiles[0];
     c.q0 = (int)(t % a.tiles[1]) * (HL_QT * a.mt);
     t /= a.tiles[1];
-    c.r0 = (int)(t % a.tiles[2]);
+    c.r0 = (int)(t % a.tiles[2]) * (a.pack2 ? 2 : 1);
     c.b = (int)(t / a.tiles[2]);
     return c;
 }
@@ -111,6 +118,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
     const int k_chunks = a.c_in / 64;
+    const int n_planes = a.pack2 ? 4 : 3;          // input planes feeding one super-tile
 
     if (warp == 0) {
         // -------- activation planes: (chunk, dR) -> one box of 10 x (16*MT + 2) voxels --------
@@ -119,7 +127,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
                 const HaloTile tc = decode_halo_tile(a, t);
                 for (int kc = 0; kc < k_chunks; ++kc)
-                    for (int dr = 0; dr < 3; ++dr) {
+                    for (int dr = 0; dr < n_planes; ++dr) {
                         mbar_wait(smem_u32(a_empty + stage), phase ^ 1);
                         const uint32_t bar = smem_u32(a_full + stage);
                         mbar_expect_tx(bar, (uint32_t)(plane_rows * 128));
@@ -136,17 +144,26 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
                 const HaloTile tc = decode_halo_tile(a, t);
                 for (int kc = 0; kc < k_chunks; ++kc)
-                    for (int tap = 0; tap < 27; ++tap) {   // tap = (dR*3 + dQ)*3 + dP in MMA order
-                        const int dp = tap % 3, dq = (tap / 3) % 3, dr = tap / 9;
-                        int k3[3];                          // tap along the tensor axes X, Y, Z
-                        k3[a.axis[0]] = dp, k3[a.axis[1]] = dq, k3[a.axis[2]] = dr;
+                    for (int tap = 0; tap < 9 * n_planes; ++tap) {   // (plane, dQ, dP) in MMA order
+                        const int dp = tap % 3, dq = (tap / 3) % 3, ip = tap / 9;
                         mbar_wait(smem_u32(b_empty + stage), phase ^ 1);
                         const uint32_t bar = smem_u32(b_full + stage);
-                        mbar_expect_tx(bar, (uint32_t)w_bytes);
-                        // weights stay packed [c_out][kX][kY][kZ][c_in], as for the per-tap kernel
-                        const int wtap = (k3[0] * 3 + k3[1]) * 3 + k3[2];
-                        tma_load_2d(smem_u32(b_base + (size_t)stage * b_bytes), &map_w, bar,
-                                    wtap * a.c_in + kc * 64, tc.n0);
+                        const uint32_t dst = smem_u32(b_base + (size_t)stage * b_bytes);
+                        // weights stay packed [c_out][kX][kY][kZ][c_in]; column of tap (dp, dq, dr):
+                        auto wcol = [&](int dr) {
+                            if (dr < 0 || dr > 2) return 27 * a.c_in;   // beyond the tensor: TMA zero fill
+                            int k3[3];                                   // tap along the tensor axes X, Y, Z
+                            k3[a.axis[0]] = dp, k3[a.axis[1]] = dq, k3[a.axis[2]] = dr;
+                            return ((k3[0] * 3 + k3[1]) * 3 + k3[2]) * a.c_in + kc * 64;
+                        };
+                        if (a.pack2) {
+                            mbar_expect_tx(bar, 2u * 64u * 128u);
+                            tma_load_2d(dst, &map_w, bar, wcol(ip), tc.n0);                 // plane r0:     dR = ip
+                            tma_load_2d(dst + 64 * 128, &map_w, bar, wcol(ip - 1), tc.n0);  // plane r0 + 1: dR = ip - 1
+                        } else {
+                            mbar_expect_tx(bar, (uint32_t)w_bytes);
+                            tma_load_2d(dst, &map_w, bar, wcol(ip), tc.n0);
+                        }
                         if (++stage == (uint32_t)a.b_stages) stage = 0, phase ^= 1;
                     }
             }
@@ -162,7 +179,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                 const uint32_t d_tmem = tmem_base + acc * acc_cols;
                 bool first = true;
                 for (int kc = 0; kc < k_chunks; ++kc)
-                    for (int dr = 0; dr < 3; ++dr) {
+                    for (int dr = 0; dr < n_planes; ++dr) {
                         mbar_wait(smem_u32(a_full + sa), pa);
                         const uint32_t plane = smem_u32(a_base + (size_t)sa * a_bytes);
                         for (int dq = 0; dq < 3; ++dq)
@@ -198,10 +215,12 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         // first, so adding it is a read-modify-write of shared memory.
         const int q4 = warp & 3;                       // TMEM lane quarter of this warp
         const int ch_local = q4 * 32 + lane;           // channel inside the n-tile
-        const bool ch_ok = ch_local < a.n_tile;
+        const bool ch_ok = a.pack2 || ch_local < a.n_tile;
         const bool epi_leader = (warp == 3 && lane == 0);
         const bool has_res = a.res != nullptr;
-        const int slabs_per_tile = a.n_tile / 64;
+        // a voxel tile is stored as 64-channel slabs: the two channel halves of a 128-channel
+        // tile, or (pack2) the 64 channels of output plane r0 and of plane r0 + 1
+        const int slabs_per_tile = a.pack2 ? 2 : a.n_tile / 64;
         const int slab_sets = a.n_slabs / slabs_per_tile;
         const int my_slab = ch_local >> 6, my_chunk = (ch_local & 63) >> 3, my_byte = (ch_local & 7) * 2;
         uint32_t xoff[8];                              // byte offset inside a slab row, by (row & 7)
@@ -222,12 +241,13 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             mbar_expect_tx(bar, (uint32_t)(slabs_per_tile * 128 * 128));
             for (int sl = 0; sl < slabs_per_tile; ++sl)
                 tma_load_5d(smem_u32(slab_base + (size_t)(into * slabs_per_tile + sl) * (128 * 128)), &map_r, bar,
-                            tc.n0 + sl * 64, tc.p0, tc.q0 + mt * HL_QT, tc.r0, tc.b);
+                            tc.n0 + (a.pack2 ? 0 : sl * 64), tc.p0, tc.q0 + mt * HL_QT, tc.r0 + (a.pack2 ? sl : 0),
+                            tc.b);
         };
 
         for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
             const HaloTile tc = decode_halo_tile(a, t);
-            const int ch = tc.n0 + ch_local;
+            const int ch = tc.n0 + (a.pack2 ? (ch_local & 63) : ch_local);
             const float sc = (a.scale && ch_ok) ? __ldg(a.scale + ch) : 1.f;
             const float sh = (a.shift && ch_ok) ? __ldg(a.shift + ch) : 0.f;
             // residual tiles are fetched while the accumulator is still being produced: all of the
@@ -277,7 +297,8 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                 if (epi_leader) {
                     for (int sl = 0; sl < slabs_per_tile; ++sl)
                         tma_store_5d(&map_y, smem_u32(slab_base + (size_t)(set * slabs_per_tile + sl) * (128 * 128)),
-                                     tc.n0 + sl * 64, tc.p0, tc.q0 + mt * HL_QT, tc.r0, tc.b);
+                                     tc.n0 + (a.pack2 ? 0 : sl * 64), tc.p0, tc.q0 + mt * HL_QT,
+                                     tc.r0 + (a.pack2 ? sl : 0), tc.b);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
                 if (++set == slab_sets) set = 0;
@@ -355,10 +376,11 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
         a.ostride[r] = out_s[perm[r]];
     }
     a.ostride_b = out_s[0] * p->out_dims[0];
-    a.stride_r = p->stride[perm[2]];
     a.tiles[0] = (a.dims[0] + HL_P - 1) / HL_P;
     a.tiles[1] = (a.dims[1] + HL_QT * mt - 1) / (HL_QT * mt);
-    a.tiles[2] = a.dims[2];
+    a.stride_r = p->stride[perm[2]];
+    a.pack2 = (a.n_tile == 64 && a.stride_r == 1) ? 1 : 0;
+    a.tiles[2] = a.pack2 ? (a.dims[2] + 1) / 2 : a.dims[2];
     a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
     a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
@@ -368,7 +390,7 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
     }
     const int plane_rows = HL_PPAD * (HL_QT * mt + 2);
     const int a_bytes = (plane_rows * 128 + 1023) & ~1023, b_bytes = 128 * 128;
-    const int slabs_per_tile = a.n_tile / 64;
+    const int slabs_per_tile = a.pack2 ? 2 : a.n_tile / 64;
     // shared memory: weight ring (16 KB stages), two sets of output slabs if they fit, the
     // rest goes to activation planes (each one feeds 36 MMAs)
     a.b_stages = 4;
@@ -399,7 +421,7 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
     {
         const cuuint64_t dims[2] = {(cuuint64_t)27 * p->c_in, (cuuint64_t)p->c_out};
         const cuuint64_t st[1] = {(cuuint64_t)27 * p->c_in * 2};
-        const cuuint32_t box[2] = {64, (cuuint32_t)a.n_tile};
+        const cuuint32_t box[2] = {64, (cuuint32_t)a.n_tile};   // pack2: two such loads fill the 128 rows
         const cuuint32_t es[2] = {1, 1};
         int rc = encode_map_bf16(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights (halo)");
         if (rc != IVX_OK) return rc;
