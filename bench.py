@@ -433,7 +433,7 @@ def run_ours(args):
         d2h = sum(o.numel() * o.element_size() for o in out0[0]) + out0[1].numel()
         del out0
         P_pinned = Pb.pin_memory()
-        e2e_steps = max(3, min(args.steps, 10))
+        e2e_steps = max(10, args.steps)      # long enough to amortise the fill / drain of the 2-deep pipeline
 
         # the call a user with host buffers makes: StreamedHotPath uploads batch i+1, computes
         # batch i and downloads batch i-1 concurrently (copy-in / compute / copy-out streams)
