@@ -148,3 +148,28 @@ def test_fast_indoor_neck_at_full_size_bf16():
         got = m(x)
     for a, b in zip(got, want):
         assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
+
+
+@pytest.mark.parametrize("name,kw,shape", [
+    ("ImVoxelNeck", dict(channels=[64, 128, 256, 512], out_channels=64, down_layers=[1, 2, 3, 4],
+                         up_layers=[3, 2, 1], conditional=False), (1, 64, 80, 80, 32)),
+    ("NuScenesImVoxelNeck", dict(in_channels=64, out_channels=256), (1, 64, 96, 104, 12)),
+])
+def test_other_necks_at_real_channel_counts_bf16(name, kw, shape):
+    """cfg5's Atlas encoder-decoder at its full 80x80x32 grid and the nuScenes neck
+    (all-axis stride-2 layer, pad (1,1,0) tail) with the tensor-core kernels."""
+    torch.manual_seed(5)
+    ref = torch_necks.NECKS[name](**kw).eval()
+    torch_necks.randomize_norms(ref, 11)
+    m = getattr(necks, name)(**kw).eval()
+    m.load_state_dict(ref.state_dict())
+    m.precision = "bf16"
+    ref.to(DEV), m.to(DEV)
+    x = torch.randn(shape, device=DEV)
+    with torch.no_grad():
+        want = ref(x)
+        got = m(x)
+    assert len(got) == len(want)
+    for a, b in zip(got, want):
+        assert a.shape == b.shape
+        assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
