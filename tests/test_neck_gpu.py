@@ -173,3 +173,34 @@ def test_other_necks_at_real_channel_counts_bf16(name, kw, shape):
     for a, b in zip(got, want):
         assert a.shape == b.shape
         assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
+
+
+def test_graphed_hot_path_replays_the_same_results():
+    """CUDA-graph replay of back-projection + neck equals the eager calls."""
+    from imvoxelnet_b200 import ops, scenes
+    from imvoxelnet_b200 import projection as pj
+    from imvoxelnet_b200.pipeline import GraphedHotPath
+    sc = scenes.scannet(n_views=5, seed=3)
+    sc.n_voxels, sc.channels = (16, 16, 8), 64
+    origin = sc.img_meta['lidar2img']['origin']
+    P = pj.compute_projection(sc.img_meta, scenes.STRIDE).to(DEV)[None]
+    h, w = sc.feat_hw
+    neck = necks.FastIndoorImVoxelNeck(64, [1, 1, 1], 64).eval().to(DEV)
+    torch_necks.randomize_norms(neck, 2)
+    neck.precision = "bf16"
+
+    def step(feats, proj):
+        vol, valid, _ = ops.backproject_scenes(feats, [(h, w)], proj, sc.n_voxels, sc.voxel_size, [origin],
+                                               out_dtype=torch.bfloat16)
+        return neck(vol), valid
+
+    graphed = GraphedHotPath(step)
+    for seed in (1, 2, 3):
+        feats = scenes.random_features(sc, seed=seed, batch=1, channels_last=True).to(DEV)
+        with torch.no_grad():
+            want, want_valid = step(feats, P)
+        got, got_valid = graphed(feats, P)
+        assert torch.equal(got_valid, want_valid)
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+    assert len(graphed._graphs) == 1
