@@ -15,6 +15,7 @@ import torch
 from torch import nn
 
 from . import backbone2d, ops
+from . import necks as _necks  # noqa: F401  (importing it registers the four 3D necks)
 from .projection import compute_projection, get_points  # noqa: F401  (get_points is re-exported: heads import it from here, imvoxel_head.py:7)
 from .registry import DETECTORS, HAVE_MMDET, NECKS, build_from, register
 
