@@ -65,9 +65,10 @@ PROTOTYPES["ivx_finalize_mean_peers"] = [c_void_p, c_void_p, c_int, c_void_p, c_
                                          c_void_p, _i64p, c_int, c_void_p, c_void_p, c_void_p]
 PROTOTYPES["ivx_conv3d_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p]
-PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"] = list(PROTOTYPES["ivx_conv3d_ndhwc"])
+PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"] = PROTOTYPES["ivx_conv3d_ndhwc"][:7] + [c_void_p, c_int64, c_void_p]
+PROTOTYPES["ivx_conv3d_tc_workspace_bytes"] = [_ConvP]
 PROTOTYPES["ivx_upsample2x_trilinear_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_int, c_void_p]
-RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64}
+RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64, "ivx_conv3d_tc_workspace_bytes": c_int64}
 
 _lib = None
 

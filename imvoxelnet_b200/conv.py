@@ -54,6 +54,7 @@ class FusedConv:
             assert tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1
         self._packed = None
         self._packed_tc = None
+        self._ws = {}
 
     # ---- parameter packing (cached until a parameter or buffer changes) ----
     def _key(self, device):
@@ -99,6 +100,17 @@ class FusedConv:
                     self._packed_tc = w.permute(0, 2, 3, 4, 1).contiguous().to(torch.bfloat16)
         return self._packed_tc, scale, shift
 
+    def _workspace(self, params, device):
+        """Split-K scratch of this layer for this geometry: zero-filled once, the kernel
+        leaves it zero-filled (include/ivx.h); None when the layer does not split."""
+        key = (str(device), params.batch, tuple(params.in_dims))
+        ws = self._ws.get(key)
+        if ws is None:
+            nbytes = _lib.lib().ivx_conv3d_tc_workspace_bytes(params)
+            ws = torch.zeros(nbytes, dtype=torch.uint8, device=device) if nbytes > 0 else False
+            self._ws[key] = ws
+        return ws if ws is not False else None
+
     def tc_eligible(self, x, out_dtype, residual=None):
         if self.transposed and residual is not None:
             return False
@@ -141,10 +153,12 @@ class FusedConv:
         with torch.cuda.device(x.device):
             if self.tc_eligible(x, out_dtype, residual):
                 wt, scale, shift = self.packed_tc(x.device)
+                ws = self._workspace(p, x.device)
                 _lib.check(_lib.lib().ivx_conv3d_ndhwc_bf16_tc(
                     p, x.data_ptr(), wt.data_ptr(), scale.data_ptr() if scale is not None else None,
-                    shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(), _stream()),
-                    "ivx_conv3d_ndhwc_bf16_tc")
+                    shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(),
+                    ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
+                    _stream()), "ivx_conv3d_ndhwc_bf16_tc")
             else:
                 _lib.check(_lib.lib().ivx_conv3d_ndhwc(
                     p, x.data_ptr(), wp.data_ptr(), scale.data_ptr() if scale is not None else None,

@@ -49,6 +49,14 @@ struct TcArgs {
     // tap's offset through an output map whose element strides are the layer stride
     int transposed;
     int up[3];                  // upsampling factor = kernel = stride of the transposed layer
+    // split-K for layers with too few tiles to fill the GPU: the k-steps of one output tile are
+    // shared by k_splits CTAs, which add their fp32 partial accumulators into `ws` with vector
+    // reductions; the CTA that arrives last (per-tile counter) reads the sums back, runs the
+    // fused epilogue and leaves workspace and counter zeroed for the next launch
+    int k_splits;
+    int steps_per_split;
+    float *ws;                  // [out tiles][128 rows][n_tile] fp32, zero on entry
+    unsigned *counters;         // [out tiles], zero on entry
 };
 
 struct TileCoord {
@@ -57,6 +65,7 @@ struct TileCoord {
 
 __device__ __forceinline__ TileCoord decode_tile(const TcArgs &a, long long t) {
     TileCoord c;
+    t /= a.k_splits;            // the split index is the fastest: CTAs of one tile run together
     c.n0 = (int)(t % a.n_splits) * a.n_tile;
     t /= a.n_splits;
     c.z0 = (int)(t % a.tiles[2]) * a.box[2];
@@ -82,6 +91,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     uint64_t *full_bar = bars, *empty_bar = bars + a.stages;
     uint64_t *acc_full = bars + 2 * a.stages, *acc_empty = acc_full + 2;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+    volatile uint32_t *split_flag = tmem_slot + 1;   // "this CTA finishes the tile" (split-K)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int tmem_cols = a.n_tile <= 16 ? 32 : (a.n_tile <= 32 ? 64 : (a.n_tile <= 64 ? 128 : (a.n_tile <= 128 ? 256 : 512)));
@@ -117,21 +127,22 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             uint32_t stage = 0, phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
                 const TileCoord tc = decode_tile(a, t);
-                for (int tap = 0; tap < n_taps; ++tap) {
+                const int k_lo = (int)(t % a.k_splits) * a.steps_per_split;
+                const int k_hi = min(k_steps, k_lo + a.steps_per_split);
+                for (int ks = k_lo; ks < k_hi; ++ks) {
+                    const int tap = ks / k_chunks, kc = ks - tap * k_chunks;
                     const int kz = tap % a.taps[2], t2 = tap / a.taps[2];
                     const int ky = t2 % a.taps[1], kx = t2 / a.taps[1];
                     const int cx = tc.x0 * a.stride[0] - a.pad[0] + kx;
                     const int cy = tc.y0 * a.stride[1] - a.pad[1] + ky;
                     const int cz = tc.z0 * a.stride[2] - a.pad[2] + kz;
-                    for (int kc = 0; kc < k_chunks; ++kc) {
-                        mbar_wait(smem_u32(empty_bar + stage), phase ^ 1);
-                        const uint32_t bar = smem_u32(full_bar + stage);
-                        const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
-                        mbar_expect_tx(bar, (uint32_t)(a.box[0] * a.box[1] * a.box[2] * 128 + b_bytes));
-                        tma_load_5d(sa, &map_x, bar, kc * TC_KCHUNK, cz, cy, cx, tc.b);
-                        tma_load_2d(sa + TC_A_BYTES, &map_w, bar, tap * a.c_in + kc * TC_KCHUNK, tc.n0);
-                        if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
-                    }
+                    mbar_wait(smem_u32(empty_bar + stage), phase ^ 1);
+                    const uint32_t bar = smem_u32(full_bar + stage);
+                    const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
+                    mbar_expect_tx(bar, (uint32_t)(a.box[0] * a.box[1] * a.box[2] * 128 + b_bytes));
+                    tma_load_5d(sa, &map_x, bar, kc * TC_KCHUNK, cz, cy, cx, tc.b);
+                    tma_load_2d(sa + TC_A_BYTES, &map_w, bar, tap * a.c_in + kc * TC_KCHUNK, tc.n0);
+                    if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
                 }
             }
         }
@@ -144,7 +155,9 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);  // epilogue drained this accumulator
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t d_tmem = tmem_base + acc * acc_stride;
-                for (int ks = 0; ks < k_steps; ++ks) {
+                const int k_lo = (int)(t % a.k_splits) * a.steps_per_split;
+                const int my_steps = min(k_steps, k_lo + a.steps_per_split) - k_lo;
+                for (int ks = 0; ks < my_steps; ++ks) {
                     mbar_wait(smem_u32(full_bar + stage), phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
@@ -178,6 +191,33 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const long long ovox = (((long long)tc.b * a.out_dims[0] + ox) * a.out_dims[1] + oy) * a.out_dims[2] + oz;
             mbar_wait(smem_u32(acc_full + acc), acc_phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            float *ws_row = nullptr;
+            if (a.k_splits > 1) {
+                // phase A (every CTA of the tile): add the partial accumulator into the workspace
+                const long long out_tile = t / a.k_splits;
+                ws_row = a.ws + (out_tile * TC_ROWS + row) * a.n_tile;
+                for (int c = 0; c < a.n_tile; c += 32) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c, v);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                    for (int j = 0; j < 32; j += 4)
+                        atomicAdd(reinterpret_cast<float4 *>(ws_row + c + j),
+                                  make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                              __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+                }
+                // the accumulator is free again; publish the partials, then count this CTA in
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(smem_u32(acc_empty + acc));
+                if (++acc == 2) acc = 0, acc_phase ^= 1;
+                __threadfence();
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (epi_leader) *split_flag = atomicAdd(a.counters + out_tile, 1u) == (unsigned)(a.k_splits - 1);
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (!*split_flag) continue;   // another CTA finishes this tile
+                __threadfence();              // phase B (last CTA): all partials are visible
+            }
             for (int c0 = 0; c0 < a.n_tile; c0 += 64) {
                 const int ncols = a.n_tile - c0 < 64 ? a.n_tile - c0 : 64;
                 uint8_t *slab_ptr = slab_base + slab * TC_A_BYTES;
@@ -186,8 +226,19 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 asm volatile("bar.sync 1, 128;" ::: "memory");
                 for (int h = 0; h < ncols; h += 32) {
                     uint32_t v[32];
-                    tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c0 + h, v);
-                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (ws_row == nullptr) {
+                        tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c0 + h, v);
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    } else {   // sums of all splits, straight from L2; leave zeros behind
+#pragma unroll
+                        for (int j = 0; j < 32; j += 4) {
+                            float4 *p4 = reinterpret_cast<float4 *>(ws_row + c0 + h + j);
+                            const float4 f4 = __ldcg(p4);
+                            __stcg(p4, make_float4(0.f, 0.f, 0.f, 0.f));
+                            v[j] = __float_as_uint(f4.x), v[j + 1] = __float_as_uint(f4.y);
+                            v[j + 2] = __float_as_uint(f4.z), v[j + 3] = __float_as_uint(f4.w);
+                        }
+                    }
                     const int ch = ch0 + c0 + h;
 #pragma unroll
                     for (int j = 0; j < 32; j += 8) {
@@ -235,6 +286,10 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
                 slab ^= 1;
+            }
+            if (ws_row != nullptr) {
+                if (epi_leader) a.counters[t / a.k_splits] = 0;   // ready for the next launch
+                continue;                                          // (accumulator already handed back)
             }
             // accumulator fully read: hand it back to the MMA warp
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -307,15 +362,13 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
 
 using namespace ivx;
 
-extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *x, const void *weight_bf16,
-                                        const float *scale, const float *shift, const void *residual,
-                                        void *y, void *stream) {
-    IVX_REQUIRE(p && x && weight_bf16 && y, "NULL argument");
+static int validate_tc(const ivx_conv3d_params *p, bool has_residual) {
+    IVX_REQUIRE(p != nullptr, "NULL params");
     if (p->in_dtype != IVX_BF16 || p->out_dtype != IVX_BF16)
         return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in and out only");
     if (p->c_in % TC_KCHUNK != 0 || p->c_out % 64 != 0)
         return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: c_in and c_out must be multiples of 64");
-    if (p->transposed && residual != nullptr)
+    if (p->transposed && has_residual)
         return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: transposed layers take no residual");
     for (int d = 0; d < 3; ++d) {
         const int expect = p->transposed ? p->in_dims[d] * p->stride[d]
@@ -328,31 +381,27 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
                         "transposed layers need kernel == stride and no padding (axis %d)", d);
     }
     IVX_REQUIRE(p->batch > 0, "batch must be positive");
-    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
-                 reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
-                "tensors must be 16-byte aligned");
+    return IVX_OK;
+}
 
-    // 3x3x3 layers (stride 1, or a stride along one axis) whose grid fills the 8 x 16*MT tiles
-    // go to the halo-reuse kernel (IVX_TC_HALO=0 keeps everything on the per-tap one)
-    {
-        static const bool halo_on = [] {
-            const char *e = getenv("IVX_TC_HALO");
-            return e == nullptr || e[0] != '0';
-        }();
-        static const int halo_max_cout = [] {
-            const char *e = getenv("IVX_HALO_MAX_COUT");
-            return e ? atoi(e) : 1024;
-        }();
-        int perm[3] = {0, 1, 2}, mt = 1;
-        // with one tile per CTA (mt == 1) an MMA covers only 128 voxels, i.e. half the tensor rate:
-        // still a win for <= 128 channels (the per-tap kernel is at half rate there too), not above
-        if (halo_on && p->c_out <= halo_max_cout && plan_halo(p, perm, &mt) >= 0.7 &&
-            (mt == 2 || p->c_out <= 128))
-            return launch_conv3d_tc_halo(p, perm, mt, x, weight_bf16, scale, shift, residual, y,
-                                         (cudaStream_t)stream);
-    }
+// does the halo-reuse kernel take this layer?  (IVX_TC_HALO=0 keeps everything on the per-tap one)
+static bool use_halo(const ivx_conv3d_params *p, int perm[3], int *mt) {
+    static const bool halo_on = [] {
+        const char *e = getenv("IVX_TC_HALO");
+        return e == nullptr || e[0] != '0';
+    }();
+    static const int halo_max_cout = [] {
+        const char *e = getenv("IVX_HALO_MAX_COUT");
+        return e ? atoi(e) : 1024;
+    }();
+    // with one tile per CTA (mt == 1) an MMA covers only 128 voxels, i.e. half the tensor rate:
+    // still a win for <= 128 channels (the per-tap kernel is at half rate there too), not above
+    return halo_on && p->c_out <= halo_max_cout && plan_halo(p, perm, mt) >= 0.7 &&
+           (*mt == 2 || p->c_out <= 128);
+}
 
-    TcArgs a;
+// tiling of the per-tap kernel, including the split-K decision
+static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     a.c_in = p->c_in, a.c_out = p->c_out;
     a.transposed = p->transposed;
     const int up_taps = p->transposed ? p->kernel[0] * p->kernel[1] * p->kernel[2] : 1;
@@ -371,9 +420,73 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
     }
     a.batch = p->batch;
     pick_box(row_dims, p->transposed ? p->stride : ld_stride, a.box, a.tiles);
-    a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
+    const long long out_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
+    // split-K: a layer with fewer tiles than ~2/3 of the SMs spreads each tile's k-steps over
+    // several CTAs (needs a workspace; the caller may not have one -> k_splits reset to 1 later)
+    const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
+    a.k_splits = 1;
+    a.steps_per_split = k_steps;
+    if (out_tiles * 3 <= kNumSMs * 2 && k_steps >= 8) {
+        int want = (int)(kNumSMs / out_tiles);
+        if (want > k_steps / 4) want = k_steps / 4;            // at least 4 k-steps per CTA
+        if (want > 1) {
+            a.steps_per_split = (k_steps + want - 1) / want;
+            a.k_splits = (k_steps + a.steps_per_split - 1) / a.steps_per_split;
+        }
+    }
+    a.n_tiles = out_tiles * a.k_splits;
+}
+
+extern "C" int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *p) {
+    if (validate_tc(p, false) != IVX_OK) return 0;
+    int perm[3] = {0, 1, 2}, mt = 1;
+    if (use_halo(p, perm, &mt)) return 0;
+    TcArgs a;
+    plan_tc(p, a);
+    if (a.k_splits <= 1) return 0;
+    const long long out_tiles = a.n_tiles / a.k_splits;
+    return out_tiles * TC_ROWS * a.n_tile * (int64_t)sizeof(float) + out_tiles * (int64_t)sizeof(unsigned);
+}
+
+extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *x, const void *weight_bf16,
+                                        const float *scale, const float *shift, const void *residual,
+                                        void *y, void *workspace, int64_t workspace_bytes, void *stream) {
+    IVX_REQUIRE(p && x && weight_bf16 && y, "NULL argument");
+    int rc0 = validate_tc(p, residual != nullptr);
+    if (rc0 != IVX_OK) return rc0;
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+                 reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    {
+        int perm[3] = {0, 1, 2}, mt = 1;
+        if (use_halo(p, perm, &mt))
+            return launch_conv3d_tc_halo(p, perm, mt, x, weight_bf16, scale, shift, residual, y,
+                                         (cudaStream_t)stream);
+    }
+
+    TcArgs a;
+    plan_tc(p, a);
+    a.ws = nullptr, a.counters = nullptr;
+    if (a.k_splits > 1) {
+        const long long out_tiles = a.n_tiles / a.k_splits;
+        const int64_t ws_floats = out_tiles * TC_ROWS * a.n_tile;
+        const int64_t need = ws_floats * (int64_t)sizeof(float) + out_tiles * (int64_t)sizeof(unsigned);
+        if (workspace != nullptr && workspace_bytes >= need &&
+            reinterpret_cast<uintptr_t>(workspace) % 16 == 0) {
+            a.ws = static_cast<float *>(workspace);
+            a.counters = reinterpret_cast<unsigned *>(a.ws + ws_floats);
+        } else {   // no (or too small a) workspace: one CTA per tile, still correct
+            a.n_tiles = out_tiles;
+            a.k_splits = 1;
+            a.steps_per_split = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
+        }
+    }
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
     a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
+    const int32_t ones[3] = {1, 1, 1};
+    const int32_t *ld_stride = p->transposed ? ones : p->stride;
+    const int up_taps = p->transposed ? p->kernel[0] * p->kernel[1] * p->kernel[2] : 1;
+    const int n_total = p->c_out * up_taps;
 
     const int stage_bytes = TC_A_BYTES + a.n_tile * 128;
     const int fixed = 2 * TC_A_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;

@@ -324,10 +324,22 @@ IVX_API int ivx_conv3d_ndhwc(const ivx_conv3d_params *params, const void *x, con
  * residual.  Returns IVX_ERR_UNSUPPORTED for shapes it does not take (c_in or
  * c_out not a multiple of 64, non-bf16 tensors): callers then use
  * ivx_conv3d_ndhwc.
+ *
+ * workspace: optional device scratch for split-K.  Layers with too few output
+ * tiles to fill the GPU (the 10x10x4 / 20x20x8 tails of the indoor necks)
+ * spread each tile's k-steps over several CTAs, which add fp32 partials into
+ * the workspace; the last CTA of a tile applies the epilogue.  It must hold
+ * ivx_conv3d_tc_workspace_bytes(params) bytes (0 = this layer does not
+ * split), be 16-byte aligned and ZERO-FILLED before its first use; every call
+ * leaves it zero-filled again, so one buffer can serve a layer forever (but
+ * not two calls that overlap on the GPU).  NULL or too small: no split.
  */
+IVX_API int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *params);
+
 IVX_API int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *params, const void *x,
                                      const void *weight_bf16, const float *scale, const float *shift,
-                                     const void *residual, void *y, void *stream);
+                                     const void *residual, void *y, void *workspace,
+                                     int64_t workspace_bytes, void *stream);
 
 /*
  * ivx_upsample2x_trilinear_ndhwc -- F.interpolate(x, scale_factor=2,

@@ -131,3 +131,29 @@ def test_tensor_core_transposed_conv(cin, cout, dims, batch):
                                    bn.running_var, bn.weight, bn.bias, False, 0.0, bn.eps))
     assert got.shape == want.shape
     assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-2, atol=1e-3)
+
+
+@pytest.mark.parametrize("cin,cout,dims,stride,batch", [(1024, 1024, (10, 10, 4), 1, 1), (1024, 128, (10, 10, 4), 1, 2),
+                                                         (512, 1024, (20, 20, 8), 2, 1), (512, 512, (20, 20, 8), 1, 1)])
+def test_split_k_tail_layers_and_workspace_reuse(cin, cout, dims, stride, batch):
+    """Few-tile layers split their k-steps over several CTAs through an fp32 workspace;
+    the workspace must come back zeroed: three calls in a row give the same result."""
+    torch.manual_seed(cout + dims[0])
+    layer = nn.Conv3d(cin, cout, 3, stride, 1, bias=False).to(DEV)
+    bn = nn.BatchNorm3d(cout).to(DEV).eval()
+    with torch.no_grad():
+        bn.running_mean.normal_(0, .1), bn.running_var.uniform_(.5, 1.5)
+        bn.weight.uniform_(.5, 1.5), bn.bias.normal_(0, .1)
+    fused = conv.FusedConv(layer, bn, relu=True)
+    x = torch.randn((batch, cin) + dims, device=DEV).to(torch.bfloat16)
+    xn = conv.to_ndhwc(x)
+    od = fused.out_dims(dims)
+    res = torch.randn((batch, cout) + od, device=DEV).to(torch.bfloat16)
+    with torch.no_grad():
+        want = _reference(x, layer, bn, True, res, False, 1.0)
+        outs = [conv.from_ndhwc(fused(xn, residual=conv.to_ndhwc(res))).float() for _ in range(3)]
+    from imvoxelnet_b200 import _lib
+    assert any(w is not False for w in fused._ws.values()), "this shape was expected to use split-K"
+    for got in outs:
+        assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-2, atol=1e-3)
+    assert torch.equal(outs[0], outs[2]) or (outs[0] - outs[2]).abs().max() < 1e-2

@@ -202,5 +202,7 @@ def test_graphed_hot_path_replays_the_same_results():
         got, got_valid = graphed(feats, P)
         assert torch.equal(got_valid, want_valid)
         for a, b in zip(got, want):
-            assert torch.equal(a, b)
+            # not bit-equal: the few-tile layers of this small neck use split-K, whose fp32
+            # partial sums are added with atomics in arrival order
+            assert_volume_close(a.float().cpu().numpy(), b.float().cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
     assert len(graphed._graphs) == 1
