@@ -67,6 +67,17 @@ PROTOTYPES["ivx_conv3d_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p
                                   c_void_p]
 PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"] = PROTOTYPES["ivx_conv3d_ndhwc"][:7] + [c_void_p, c_int64, c_void_p]
 PROTOTYPES["ivx_conv3d_tc_workspace_bytes"] = [_ConvP]
+c_float = ctypes.c_float
+PROTOTYPES["ivx_channel_moments_ndhwc"] = [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p]
+PROTOTYPES["ivx_affine_act_ndhwc"] = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_int64,
+                                      c_int, c_void_p, c_void_p]
+PROTOTYPES["ivx_affine_act_backward_ndhwc"] = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int,
+                                               c_float, c_int64, c_int, c_void_p, c_void_p, c_void_p]
+PROTOTYPES["ivx_channel_lincomb_ndhwc"] = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int,
+                                           c_void_p, c_void_p]
+PROTOTYPES["ivx_conv3d_dgrad_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p]
+PROTOTYPES["ivx_conv3d_wgrad_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p]
+PROTOTYPES["ivx_upsample2x_trilinear_backward_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_void_p]
 PROTOTYPES["ivx_upsample2x_trilinear_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_int, c_void_p]
 RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64, "ivx_conv3d_tc_workspace_bytes": c_int64}
 

@@ -125,11 +125,31 @@ class FusedConv:
             return tuple(i * st for i, st in zip(in_dims, s))
         return tuple((i + 2 * pd - kk) // st + 1 for i, pd, kk, st in zip(in_dims, p, k, s))
 
+    def make_params(self, b, in_dims, od, cin, cout, *, relu, after, post, in_dtype, out_dtype):
+        """``ivx_conv3d_params`` of this layer for one input geometry."""
+        p = _lib.ConvParams()
+        p.batch, p.c_in, p.c_out = b, cin, cout
+        k, s, pd = _triple(self.conv.kernel_size), _triple(self.conv.stride), _triple(self.conv.padding)
+        for d in range(3):
+            p.in_dims[d], p.out_dims[d] = in_dims[d], od[d]
+            p.kernel[d], p.stride[d], p.pad[d] = k[d], s[d], pd[d]
+        p.transposed, p.relu = int(self.transposed), int(relu)
+        p.residual_after_act, p.post_scale = int(after), float(post)
+        p.in_dtype, p.out_dtype = in_dtype, out_dtype
+        return p
+
+    def wants_autograd(self, x):
+        """Training path: the module is in ``.train()`` mode, or a gradient is wanted for x."""
+        return torch.is_grad_enabled() and (self.conv.training or x.requires_grad)
+
     def __call__(self, x, residual=None, residual_after_act=False, post_scale=1.0, out_dtype=None):
         """x: [B,X,Y,Z,Cin] dense CUDA tensor -> [B,X',Y',Z',Cout]."""
         global _launches
         if not x.is_cuda:
             raise _lib.IvxError("the 3D-neck kernels need CUDA tensors: there is no CPU implementation")
+        if self.wants_autograd(x):
+            from . import train
+            return train.fused_layer_train(self, x, residual, residual_after_act, post_scale)
         assert x.is_contiguous() and x.dim() == 5
         b, in_dims, cin = x.shape[0], tuple(x.shape[1:4]), x.shape[4]
         cout = self.conv.out_channels
@@ -138,15 +158,8 @@ class FusedConv:
         out_dtype = out_dtype or x.dtype
         y = torch.empty((b,) + od + (cout,), dtype=out_dtype, device=x.device)
         wp, scale, shift = self.packed(x.device)
-        p = _lib.ConvParams()
-        p.batch, p.c_in, p.c_out = b, cin, cout
-        k, s, pd = _triple(self.conv.kernel_size), _triple(self.conv.stride), _triple(self.conv.padding)
-        for d in range(3):
-            p.in_dims[d], p.out_dims[d] = in_dims[d], od[d]
-            p.kernel[d], p.stride[d], p.pad[d] = k[d], s[d], pd[d]
-        p.transposed, p.relu = int(self.transposed), int(self.relu)
-        p.residual_after_act, p.post_scale = int(residual_after_act), float(post_scale)
-        p.in_dtype, p.out_dtype = _DT[x.dtype], _DT[out_dtype]
+        p = self.make_params(b, in_dims, od, cin, cout, relu=self.relu, after=residual_after_act,
+                             post=post_scale, in_dtype=_DT[x.dtype], out_dtype=_DT[out_dtype])
         if residual is not None:
             assert residual.shape == y.shape and residual.dtype == y.dtype and residual.is_contiguous()
         res_ptr = residual.data_ptr() if residual is not None else None
@@ -171,7 +184,11 @@ class FusedConv:
 def upsample2x_trilinear(x):
     """F.interpolate(scale_factor=2, mode='trilinear', align_corners=False) on [B,X,Y,Z,C]."""
     global _launches
-    assert x.is_cuda and x.is_contiguous() and x.dim() == 5
+    assert x.is_cuda and x.dim() == 5
+    if torch.is_grad_enabled() and x.requires_grad:
+        from . import train
+        return train.upsample2x_train(x)
+    assert x.is_contiguous()
     b, xs, ys, zs, c = x.shape
     y = torch.empty((b, 2 * xs, 2 * ys, 2 * zs, c), dtype=x.dtype, device=x.device)
     with torch.cuda.device(x.device):

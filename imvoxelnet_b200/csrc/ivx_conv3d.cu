@@ -30,6 +30,7 @@ struct ConvArgs {
     long long m_total;   // GEMM rows: output voxels (input voxels if transposed)
     int n_cols;
     int taps;
+    int dgrad;           // gather for the data gradient: source voxel = (row + pad - tap) / stride when divisible
 };
 
 template <typename T>
@@ -113,9 +114,17 @@ __global__ void __launch_bounds__(256) conv3d_simt_kernel(const __grid_constant_
             } else {
                 const int kz = tap % p.kernel[2], t2 = tap / p.kernel[2];
                 const int ky = t2 % p.kernel[1], kx = t2 / p.kernel[1];
-                const int xi = ax * p.stride[0] - p.pad[0] + kx;
-                const int yi = ay * p.stride[1] - p.pad[1] + ky;
-                const int zi = az * p.stride[2] - p.pad[2] + kz;
+                int xi = ax * p.stride[0] - p.pad[0] + kx;
+                int yi = ay * p.stride[1] - p.pad[1] + ky;
+                int zi = az * p.stride[2] - p.pad[2] + kz;
+                if (a.dgrad) {   // rows are input-gradient voxels; which output voxel used them with this tap?
+                    const int qx = ax + p.pad[0] - kx, qy = ay + p.pad[1] - ky, qz = az + p.pad[2] - kz;
+                    const bool hit = qx >= 0 && qy >= 0 && qz >= 0 && qx % p.stride[0] == 0 &&
+                                     qy % p.stride[1] == 0 && qz % p.stride[2] == 0;
+                    xi = hit ? qx / p.stride[0] : -1;
+                    yi = qy / p.stride[1];
+                    zi = qz / p.stride[2];
+                }
                 if (xi >= 0 && xi < p.in_dims[0] && yi >= 0 && yi < p.in_dims[1] && zi >= 0 &&
                     zi < p.in_dims[2])
                     in_off = (((long long)ab * p.in_dims[0] + xi) * p.in_dims[1] + yi) * p.in_dims[2] + zi;
@@ -275,6 +284,7 @@ extern "C" int ivx_conv3d_ndhwc(const ivx_conv3d_params *params, const void *x, 
     a.m_total = (long long)p.batch * rd[0] * rd[1] * rd[2];
     a.n_cols = p.transposed ? ktaps * p.c_out : p.c_out;
     a.taps = p.transposed ? 1 : ktaps;
+    a.dgrad = 0;
     const long long gx = (a.m_total + BM - 1) / BM;
     IVX_REQUIRE(gx < (1ll << 31), "too many output voxels");
     dim3 grid((unsigned)gx, (unsigned)((a.n_cols + BN - 1) / BN));
@@ -310,5 +320,33 @@ extern "C" int ivx_upsample2x_trilinear_ndhwc(const void *x, void *y, int batch,
             static_cast<const __nv_bfloat16 *>(x), static_cast<__nv_bfloat16 *>(y), batch, in_dims[0],
             in_dims[1], in_dims[2], n_channels / 4);
     IVX_CHECK_LAUNCH("upsample launch");
+    return IVX_OK;
+}
+
+// Data gradient of a (non-transposed) convolution, fp32: for every input voxel, gather the output
+// gradients that used it.  Same kernel as the forward pass with the channel roles exchanged.
+extern "C" int ivx_conv3d_dgrad_ndhwc(const ivx_conv3d_params *params, const float *grad_y,
+                                      const float *weight_t, float *grad_x, void *stream) {
+    int rc = validate_conv(params);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(grad_y && weight_t && grad_x, "NULL argument");
+    IVX_REQUIRE(!params->transposed, "transposed layers: their data gradient is a plain strided convolution");
+    ConvArgs a;
+    a.p = *params;
+    ivx_conv3d_params &q = a.p;   // the gather runs over the INPUT grid and reads the OUTPUT grid
+    q.c_in = params->c_out, q.c_out = params->c_in;
+    for (int d = 0; d < 3; ++d) q.in_dims[d] = params->out_dims[d], q.out_dims[d] = params->in_dims[d];
+    q.relu = 0, q.residual_after_act = 0, q.post_scale = 1.f;
+    q.in_dtype = q.out_dtype = IVX_F32;
+    a.x = grad_y, a.w = weight_t, a.scale = nullptr, a.shift = nullptr, a.res = nullptr, a.y = grad_x;
+    a.m_total = (long long)q.batch * q.out_dims[0] * q.out_dims[1] * q.out_dims[2];
+    a.n_cols = q.c_out;
+    a.taps = q.kernel[0] * q.kernel[1] * q.kernel[2];
+    a.dgrad = 1;
+    const long long gx = (a.m_total + BM - 1) / BM;
+    IVX_REQUIRE(gx < (1ll << 31), "too many voxels");
+    dim3 grid((unsigned)gx, (unsigned)((a.n_cols + BN - 1) / BN));
+    conv3d_simt_kernel<float, float><<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    IVX_CHECK_LAUNCH("conv3d dgrad launch");
     return IVX_OK;
 }

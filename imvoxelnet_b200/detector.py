@@ -133,9 +133,16 @@ class ImVoxelNet(_Base):
         return self.forward_test(img, img_metas, **kwargs)
 
     def forward_train(self, img, img_metas, gt_bboxes_3d, gt_labels_3d, **kwargs):
-        raise NotImplementedError(
-            "training through the fused kernels (autograd of backproject, BN batch statistics) is "
-            "SURVEY.md section 8(f)-1 and not implemented; use the reference for training")
+        """As upstream (:82-87).  The hot path is differentiable: the fused back-projection has
+        a backward kernel and the necks run batch-statistics BatchNorm + autograd through this
+        library's fp32 kernels (``precision`` must be "fp32"); the heads are the reference's."""
+        if self.bbox_head is None:
+            raise RuntimeError("no bbox_head was built (mmdet3d heads are not available here)")
+        x, valids, features_2d = self.extract_feat(img, img_metas, 'train')
+        losses = self.bbox_head.forward_train(x, valids.float(), img_metas, gt_bboxes_3d, gt_labels_3d)
+        if self.head_2d is not None:
+            losses.update(self.head_2d.loss(*features_2d, img_metas))
+        return losses
 
     def forward_test(self, img, img_metas, **kwargs):
         return self.simple_test(img, img_metas)

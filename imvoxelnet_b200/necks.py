@@ -7,9 +7,10 @@ The module tree mirrors the reference's attribute names exactly
 ``conv_blocks``; ``model.{0..5}``) so released checkpoints load unchanged; the
 ``nn.Conv3d`` / ``nn.BatchNorm3d`` children only hold parameters.
 
-Training mode (BatchNorm batch statistics, autograd) is SURVEY.md section
-8(f)-1 and not implemented: ``forward`` raises in ``.train()`` mode rather than
-silently running something else.
+In ``.train()`` mode (fp32 only) the same layers run through ``train.py``:
+BatchNorm with batch statistics (running statistics updated as nn.BatchNorm3d
+does) and autograd, every forward and backward step a kernel of this library
+(SURVEY.md section 8(f)-1).
 """
 import torch
 from torch import nn
@@ -31,12 +32,12 @@ class _NeckBase(nn.Module):
         pass
 
     def _enter(self, x):
-        if self.training:
-            raise NotImplementedError(
-                f"{type(self).__name__}: training mode is not implemented (eval-mode kernels only); "
-                "call .eval()")
         if self.precision not in PRECISIONS:
             raise ValueError(f"precision must be one of {PRECISIONS}")
+        if self.training and torch.is_grad_enabled() and self.precision != "fp32":
+            raise NotImplementedError(
+                f"{type(self).__name__}: training runs in fp32 (batch-statistics BatchNorm and autograd "
+                "through the CUDA-core kernels); set precision='fp32'")
         y = to_ndhwc(x)
         return y.to(torch.bfloat16) if self.precision == "bf16" else y.float()
 

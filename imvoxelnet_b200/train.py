@@ -1,0 +1,192 @@
+"""Training mode of the fused neck layers: batch-statistics BatchNorm and autograd.
+
+The reference trains its necks with ordinary PyTorch autograd
+(``forward_train``, mmdet3d/models/detectors/imvoxelnet.py:82-87; BatchNorm3d
+in ``.train()`` mode normalises with the batch moments and updates the running
+statistics).  Here every fused layer of ``conv.FusedConv`` becomes one
+``torch.autograd.Function`` whose forward and backward are made of the fp32
+CUDA kernels declared under "training mode" in include/ivx.h; only vectors of
+length C (BN coefficients) are handled with torch ops.
+"""
+import ctypes
+
+import torch
+from torch import nn
+
+from . import _lib
+
+_F32 = _lib.IVX_F32
+_launches = 0
+
+
+def launch_count():
+    return _launches
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return t.data_ptr() if t is not None else None
+
+
+def _call(name, *args):
+    global _launches
+    _lib.check(getattr(_lib.lib(), name)(*args, _stream()), name)
+    _launches += 1
+
+
+def _moments(a, b, rows, c):
+    """(sum a, sum a*b) per channel, accumulated in double."""
+    acc = torch.zeros(2 * c, dtype=torch.float64, device=a.device)
+    _call("ivx_channel_moments_ndhwc", a.data_ptr(), b.data_ptr(), rows, c, acc.data_ptr())
+    return acc[:c], acc[c:]
+
+
+def _copy_params(p, **changes):
+    q = _lib.ConvParams()
+    ctypes.memmove(ctypes.byref(q), ctypes.byref(p), ctypes.sizeof(q))
+    for k, v in changes.items():
+        if isinstance(v, (tuple, list)):
+            for d in range(3):
+                getattr(q, k)[d] = v[d]
+        else:
+            setattr(q, k, v)
+    return q
+
+
+class _FusedLayer(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, gamma, beta, residual, fc, after, post):
+        conv, bn = fc.conv, fc.bn
+        dev = x.device
+        b, in_dims, cin = x.shape[0], tuple(x.shape[1:4]), x.shape[4]
+        cout = conv.out_channels
+        od = fc.out_dims(in_dims)
+        p = fc.make_params(b, in_dims, od, cin, cout, relu=0, after=0, post=1.0, in_dtype=_F32, out_dtype=_F32)
+        w = weight.detach().float()
+        wp = (w.permute(0, 2, 3, 4, 1) if fc.transposed else w.permute(2, 3, 4, 1, 0)).contiguous()
+        z = torch.empty((b,) + od + (cout,), dtype=torch.float32, device=dev)
+        bias_f = bias.detach().float().contiguous() if bias is not None else None
+        _call("ivx_conv3d_ndhwc", p, x.data_ptr(), wp.data_ptr(), None, _ptr(bias_f), None, z.data_ptr())
+        rows = z.numel() // cout
+        sc = sh = mean = invstd = None
+        batch_stats = bn is not None and bn.training
+        if bn is not None:
+            if batch_stats:
+                s1, s2 = _moments(z, z, rows, cout)
+                mean64 = s1 / rows
+                var64 = (s2 / rows - mean64 * mean64).clamp_(min=0)
+                mean, invstd = mean64.float(), torch.rsqrt(var64 + bn.eps).float()
+                if bn.track_running_stats and bn.running_mean is not None:
+                    with torch.no_grad():
+                        bn.num_batches_tracked += 1
+                        m = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+                        bn.running_mean.mul_(1 - m).add_(mean, alpha=m)
+                        bn.running_var.mul_(1 - m).add_((var64 * (rows / max(rows - 1, 1))).float(), alpha=m)
+            else:
+                mean = bn.running_mean.detach().float()
+                invstd = torch.rsqrt(bn.running_var.detach().float() + bn.eps)
+            sc = (gamma.detach().float() * invstd).contiguous()
+            sh = (beta.detach().float() - mean * sc).contiguous()
+        trivial = bn is None and not fc.relu and residual is None and post == 1.0
+        if trivial:
+            y = z
+        else:
+            y = torch.empty_like(z)
+            _call("ivx_affine_act_ndhwc", z.data_ptr(), _ptr(sc), _ptr(sh), _ptr(residual), int(fc.relu),
+                  int(after), float(post), rows, cout, y.data_ptr())
+        ctx.fc, ctx.p, ctx.flags = fc, p, (after, post, trivial, batch_stats, rows)
+        ctx.has_bias = bias is not None
+        keep_res = residual if (residual is not None and fc.relu and not after) else None
+        ctx.has_res = residual is not None
+        ctx.save_for_backward(x, wp, z, sc, sh, mean, invstd, keep_res)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        fc, p = ctx.fc, ctx.p
+        after, post, trivial, batch_stats, rows = ctx.flags
+        x, wp, z, sc, sh, mean, invstd, res = ctx.saved_tensors
+        cout, cin = p.c_out, p.c_in
+        dy = dy.contiguous().float()
+        dres = None
+        if trivial:
+            g = dy
+        else:
+            g = torch.empty_like(z)
+            g_after = torch.empty_like(z) if (ctx.has_res and after) else None
+            _call("ivx_affine_act_backward_ndhwc", dy.data_ptr(), z.data_ptr(), _ptr(sc), _ptr(sh), _ptr(res),
+                  int(fc.relu), int(after), float(post), rows, cout, g.data_ptr(), _ptr(g_after))
+            if ctx.has_res:
+                dres = g_after if after else g
+        dgamma = dbeta = None
+        if fc.bn is not None:
+            s1, s2 = _moments(g, z, rows, cout)                    # sum g, sum g*z
+            inv64, mean64 = invstd.double(), mean.double()
+            s2h = inv64 * (s2 - mean64 * s1)                       # sum g * x_hat
+            dbeta, dgamma = s1.float(), s2h.float()
+            if batch_stats:
+                sc64 = sc.double()
+                A = sc
+                B = (-sc64 * inv64 * s2h / rows).float()
+                C = (-sc64 * s1 / rows + sc64 * inv64 * mean64 * s2h / rows).float()
+            else:                                                   # frozen statistics: dz = sc * g
+                A, B, C = sc, torch.zeros_like(sc), torch.zeros_like(sc)
+            dz = torch.empty_like(z)
+            _call("ivx_channel_lincomb_ndhwc", g.data_ptr(), z.data_ptr(), A.contiguous().data_ptr(),
+                  B.contiguous().data_ptr(), C.contiguous().data_ptr(), rows, cout, dz.data_ptr())
+        else:
+            dz = g
+        dbias = None
+        if ctx.has_bias:
+            dbias = _moments(dz, dz, rows, cout)[0].float()
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            if fc.transposed:    # data gradient of a kernel == stride transposed conv: a plain strided conv of dz
+                q = _copy_params(p, c_in=cout, c_out=cin, in_dims=tuple(p.out_dims), out_dims=tuple(p.in_dims),
+                                 transposed=0)
+                wt = wp.permute(1, 2, 3, 4, 0).contiguous()        # [Cin,k,k,k,Cout] -> [taps][Cout][Cin]
+                _call("ivx_conv3d_ndhwc", q, dz.data_ptr(), wt.data_ptr(), None, None, None, dx.data_ptr())
+            else:
+                wt = wp.permute(0, 1, 2, 4, 3).contiguous()        # [taps][Cin][Cout] -> [taps][Cout][Cin]
+                _call("ivx_conv3d_dgrad_ndhwc", p, dz.data_ptr(), wt.data_ptr(), dx.data_ptr())
+        dwp = torch.zeros_like(wp)
+        _call("ivx_conv3d_wgrad_ndhwc", p, x.data_ptr(), dz.data_ptr(), dwp.data_ptr())
+        dw = dwp.permute(0, 4, 1, 2, 3) if fc.transposed else dwp.permute(4, 3, 0, 1, 2)
+        return dx, dw.contiguous(), dbias, dgamma, dbeta, dres, None, None, None
+
+
+def fused_layer_train(fc, x, residual=None, residual_after_act=False, post_scale=1.0):
+    """Differentiable forward of a ``FusedConv`` (fp32 channels-last tensors)."""
+    if x.dtype != torch.float32:
+        raise NotImplementedError("training runs in fp32: set precision='fp32' on the neck")
+    bn = fc.bn
+    return _FusedLayer.apply(x.contiguous(), fc.conv.weight, fc.conv.bias,
+                             bn.weight if bn is not None else None, bn.bias if bn is not None else None,
+                             residual.contiguous() if residual is not None else None, fc,
+                             bool(residual_after_act), float(post_scale))
+
+
+class _Upsample2x(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        b, xs, ys, zs, c = x.shape
+        y = torch.empty((b, 2 * xs, 2 * ys, 2 * zs, c), dtype=x.dtype, device=x.device)
+        _call("ivx_upsample2x_trilinear_ndhwc", x.data_ptr(), y.data_ptr(), b, c, _lib.i32([xs, ys, zs]), _F32)
+        ctx.shape = tuple(x.shape)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        b, xs, ys, zs, c = ctx.shape
+        dx = torch.zeros(ctx.shape, dtype=torch.float32, device=dy.device)
+        _call("ivx_upsample2x_trilinear_backward_ndhwc", dy.contiguous().data_ptr(), dx.data_ptr(), b, c,
+              _lib.i32([xs, ys, zs]))
+        return dx
+
+
+def upsample2x_train(x):
+    return _Upsample2x.apply(x.contiguous())

@@ -351,6 +351,61 @@ IVX_API int ivx_upsample2x_trilinear_ndhwc(const void *x, void *y, int batch, in
                                            const int32_t *in_dims /* host[3] */, int dtype,
                                            void *stream);
 
+/* ----------------------- 3D neck, training mode (fp32) ----------------------- */
+
+/*
+ * In training (forward_train, detectors/imvoxelnet.py:82-87) BatchNorm3d uses
+ * batch statistics and autograd runs through every layer of
+ * necks/imvoxelnet.py.  A fused layer is then computed as
+ *   z = conv(x) + bias                      ivx_conv3d_ndhwc (scale NULL, shift = bias, no ReLU)
+ *   S1, S2 = sum z, sum z*z per channel     ivx_channel_moments_ndhwc  -> batch mean / variance
+ *   y = post * (relu(z*sc + sh [+res]) [+res])   ivx_affine_act_ndhwc, sc/sh from the batch moments
+ * and differentiated with
+ *   g (= dL/du), g_after                    ivx_affine_act_backward_ndhwc
+ *   sum g, sum g*z per channel              ivx_channel_moments_ndhwc   -> d gamma, d beta
+ *   dz = A_c*g + B_c*z + C_c                ivx_channel_lincomb_ndhwc   (BatchNorm backward, closed form)
+ *   dx                                      ivx_conv3d_dgrad_ndhwc (transposed layers: ivx_conv3d_ndhwc)
+ *   dW                                      ivx_conv3d_wgrad_ndhwc
+ * All tensors fp32, channels-last, dense: [rows][C] with rows = batch * X * Y * Z.
+ */
+
+/* acc[c] += sum_r a[r][c];  acc[C + c] += sum_r a[r][c] * b[r][c]   (acc: 2*C doubles, caller-zeroed) */
+IVX_API int ivx_channel_moments_ndhwc(const float *a, const float *b, int64_t rows, int n_channels,
+                                      double *acc, void *stream);
+
+/* y = post_scale * (act(z * scale + shift [+ residual]) [+ residual]); scale / shift / residual may be NULL */
+IVX_API int ivx_affine_act_ndhwc(const float *z, const float *scale, const float *shift,
+                                 const float *residual, int relu, int residual_after_act,
+                                 float post_scale, int64_t rows, int n_channels, float *y, void *stream);
+
+/* grad_u = gradient w.r.t. u = z*scale + shift (also that of a residual added before the activation);
+ * grad_after (may be NULL) = post_scale * grad_y, the gradient of a residual added after it */
+IVX_API int ivx_affine_act_backward_ndhwc(const float *grad_y, const float *z, const float *scale,
+                                          const float *shift, const float *residual, int relu,
+                                          int residual_after_act, float post_scale, int64_t rows,
+                                          int n_channels, float *grad_u, float *grad_after, void *stream);
+
+/* out[r][c] = A[c] * g[r][c] + B[c] * z[r][c] + C[c] */
+IVX_API int ivx_channel_lincomb_ndhwc(const float *g, const float *z, const float *A, const float *B,
+                                      const float *C, int64_t rows, int n_channels, float *out,
+                                      void *stream);
+
+/* grad_x [batch][in_dims][c_in] of a (non-transposed) layer from grad_y [batch][out_dims][c_out];
+ * weight_t: fp32 [kX*kY*kZ][c_out][c_in].  params describe the FORWARD layer. */
+IVX_API int ivx_conv3d_dgrad_ndhwc(const ivx_conv3d_params *params, const float *grad_y,
+                                   const float *weight_t, float *grad_x, void *stream);
+
+/* grad_w += x^T * grad_z in the layout of ivx_conv3d_ndhwc's weight ([taps][c_in][c_out];
+ * transposed layers [c_in][taps][c_out]); grad_w must be zero-filled by the caller (fp32 atomics) */
+IVX_API int ivx_conv3d_wgrad_ndhwc(const ivx_conv3d_params *params, const float *x, const float *grad_z,
+                                   float *grad_w, void *stream);
+
+/* grad_x [batch][X][Y][Z][C] += transpose of ivx_upsample2x_trilinear_ndhwc applied to grad_y
+ * [batch][2X][2Y][2Z][C]; grad_x must be zero-filled by the caller */
+IVX_API int ivx_upsample2x_trilinear_backward_ndhwc(const float *grad_y, float *grad_x, int batch,
+                                                    int n_channels, const int32_t *in_dims /* host[3] */,
+                                                    void *stream);
+
 #ifdef __cplusplus
 }
 #endif

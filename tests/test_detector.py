@@ -107,3 +107,28 @@ def test_extract_feat_matches_the_reference_loop(precision):
     for a, b in zip(outs, want):
         assert a.shape == b.shape
         assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=rel, atol=1e-6 if precision == "fp32" else 1e-3)
+
+
+@pytest.mark.gpu
+def test_extract_feat_is_differentiable_in_training_mode():
+    """images -> 2D net -> fused back-projection -> neck, all under autograd: the loss
+    gradient reaches the 2D backbone and the neck parameters (forward_train, :82-87)."""
+    dev = "cuda:0"
+    torch.manual_seed(0)
+    sc = scenes.scannet(n_views=2, seed=2)
+    sc.img_meta['img_shape'] = (96, 128, 3)
+    sc.img_meta['ori_shape'] = (480, 640, 3)
+    m = _build(dict(KITTI_MODEL, neck=dict(type='FPN', in_channels=[256, 512, 1024, 2048], out_channels=16,
+                                           num_outs=4),
+                    neck_3d=dict(type='FastIndoorImVoxelNeck', in_channels=16, n_blocks=[1, 1, 1],
+                                 out_channels=8),
+                    n_voxels=(8, 8, 8), voxel_size=(.6, .6, .4)))
+    m = m.train().to(dev)
+    img = torch.randn(2, 2, 3, 96, 128, device=dev)
+    outs, valids, _ = m.extract_feat(img, [sc.img_meta, sc.img_meta], 'train')
+    assert valids.any()
+    sum(o.square().mean() for o in outs).backward()
+    g_neck = m.neck_3d.down_layer_0[0].conv1.weight.grad
+    g_2d = m.backbone.conv1.weight.grad
+    assert g_neck is not None and torch.isfinite(g_neck).all() and float(g_neck.abs().max()) > 0
+    assert g_2d is not None and torch.isfinite(g_2d).all() and float(g_2d.abs().max()) > 0

@@ -67,7 +67,9 @@ def test_product_necks_share_the_reference_state_dict_layout():
 def test_necks_refuse_cpu_and_training_mode():
     from imvoxelnet_b200 import _lib, necks
     m = necks.KittiImVoxelNeck(4, 8)
+    m.precision = "bf16"                      # training is fp32 only
     with pytest.raises(NotImplementedError):
         m.train()(torch.zeros(1, 4, 4, 4, 12))
+    m.precision = "fp32"
     with pytest.raises(_lib.IvxError):
         m.eval()(torch.zeros(1, 4, 4, 4, 12))
