@@ -47,9 +47,31 @@ def main():
     ap.add_argument("--precision", default="bf16")
     ap.add_argument("--layers", action="store_true")
     ap.add_argument("--torch-ref", action="store_true")
+    ap.add_argument("--train", action="store_true", help="time forward + backward in training mode (fp32)")
     args = ap.parse_args()
     kw, shape, gflop = CONFIGS[args.neck]
     dev = "cuda:0"
+    if args.train:
+        from oracle import torch_necks
+        torch.backends.cudnn.allow_tf32 = False
+        torch.manual_seed(0)
+        ref = torch_necks.NECKS[args.neck](**kw).to(dev).train()
+        mine = getattr(necks, args.neck)(**kw).to(dev).train()
+        mine.load_state_dict(ref.state_dict())
+        x = torch.randn((args.batch,) + shape, device=dev).contiguous(memory_format=torch.channels_last_3d)
+
+        def step(m, inp):
+            m.zero_grad(set_to_none=True)
+            xin = inp.clone().requires_grad_(True)
+            sum(o.float().square().mean() for o in m(xin)).backward()
+
+        out = {"neck": args.neck, "batch": args.batch, "mode": "train fwd+bwd, fp32"}
+        out["ours_ms"] = timed(lambda: step(mine, x), reps=3, warm=1)
+        out["torch_cudnn_fp32_ms"] = timed(lambda: step(ref, x.contiguous()), reps=3, warm=1)
+        torch.backends.cudnn.allow_tf32 = True
+        out["torch_cudnn_tf32_ms"] = timed(lambda: step(ref, x.contiguous()), reps=3, warm=1)
+        print(json.dumps(out))
+        return
     torch.manual_seed(0)
     m = getattr(necks, args.neck)(**kw).eval().to(dev)
     m.precision = args.precision
