@@ -290,6 +290,13 @@ def run_ours(args):
     dev_sets = [host_pinned.to(dev) for _ in range(n_sets)]
     for i, d in enumerate(dev_sets):
         d.add_(float(i))  # different contents, same layout
+    feat_bytes = 4
+    if args.feature_dtype == "bf16":
+        dev_sets = [d.to(torch.bfloat16) for d in dev_sets]
+        host_pinned = _pinned_like(dev_sets[0])
+        host_pinned.copy_(dev_sets[0])
+        feat_bytes = 2
+        b_algo -= U * C * 2            # the gathered pixels are half as wide
     Pb = P[my_views].unsqueeze(0).expand(batch, Vr, 3, 4).contiguous()
     P_dev = Pb.to(dev)
     hws = [(h, w)] * batch
@@ -429,7 +436,7 @@ def run_ours(args):
     # ---- end to end: host buffers in, host buffers out, every step ----
     with torch.no_grad():
         out0 = step(0)
-        h2d = host_pinned.numel() * 4 + Pb.numel() * 4
+        h2d = host_pinned.numel() * feat_bytes + Pb.numel() * 4
         d2h = sum(o.numel() * o.element_size() for o in out0[0]) + out0[1].numel()
         del out0
         P_pinned = Pb.pin_memory()
@@ -501,7 +508,7 @@ def run_ours(args):
                                 if view_sharded
                                 else f"scenes data-parallel x{world}, no collective"),
                 "l2": f"{n_sets} rotating input sets; activations written per step >> 126 MB L2",
-                "layout": "features NHWC fp32, volume and neck activations NDHWC"}),
+                "layout": f"features NHWC {args.feature_dtype}, volume and neck activations NDHWC"}),
             "scenes_per_s": scenes_global / (ms_per_step * 1e-3),
             "stages": stages,
             "timing": {"mode": "cuda-graph replay of K steps, median of 5" if use_graph else "eager",
@@ -547,6 +554,8 @@ def main():
     ap.add_argument("--neck-precision", default="bf16", choices=["bf16", "fp32"],
                     help="bf16: tcgen05 kernels (1e-2 of the reference); fp32: CUDA-core parity path (1e-5)")
     ap.add_argument("--no-neck", action="store_true", help="time the back-projection stage only")
+    ap.add_argument("--feature-dtype", default="f32", choices=["f32", "bf16"],
+                    help="dtype of the 2D feature maps (the reference's are fp32; bf16 halves the gather)")
     ap.add_argument("--collective", default="auto", choices=["auto", "multimem", "peer", "nccl"],
                     help="view-sharded mode (scannet_fast, N > 1): how the partial sums are reduced")
     args = ap.parse_args()

@@ -59,6 +59,7 @@ PROTOTYPES = {
 }
 PROTOTYPES["ivx_backproject_scenes_nchw_noalloc"] = PROTOTYPES["ivx_backproject_scenes_nchw"][:17] + [c_void_p]
 IVX_NOALLOC_SCRATCH_BYTES = 32 * 1024 * 1024
+PROTOTYPES["ivx_backproject_scenes_bf16"] = list(PROTOTYPES["ivx_backproject_scenes"])
 PROTOTYPES["ivx_backproject_scenes_backward"] = [c_void_p, _i64p, c_void_p, _i64p, c_int, c_int, c_int, _i32p,
                                                  c_void_p, c_void_p, _GridP, _f32p, c_int64, c_int, c_void_p]
 PROTOTYPES["ivx_finalize_mean_peers"] = [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int64,

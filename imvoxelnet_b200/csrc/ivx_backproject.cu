@@ -56,7 +56,8 @@ static FastDiv make_fastdiv(int d) {
 }
 
 struct BpArgs {
-    const float *feat;
+    const float *feat;                       // (bf16 maps: same pointer, see feat_bf16)
+    int feat_bf16;                           // 1: the maps are bf16 (vectorised kernel only)
     long long fs_b, fs_v, fs_c, fs_h, fs_w;  // element strides of [B][V][C][H][W]
     int q_v, q_h, q_w;                       // the same in float4 units (vectorised kernel)
     const float *proj;                       // [B][V][12]
@@ -204,12 +205,21 @@ __device__ __forceinline__ void zero4(float4 (&acc)[CPL]) {
 }
 
 template <int G, int CPL>
-__device__ __forceinline__ void gather4(const float4 *feat4, int off, int t, const bool (&ch_ok)[CPL],
+__device__ __forceinline__ void gather4(const void *feat, bool bf16, int off, int t, const bool (&ch_ok)[CPL],
                                         float4 (&r)[CPL]) {
 #pragma unroll
     for (int i = 0; i < CPL; ++i) {
         r[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (off >= 0 && ch_ok[i]) r[i] = __ldg(feat4 + off + t + i * G);
+        if (off >= 0 && ch_ok[i]) {
+            if (!bf16) {
+                r[i] = __ldg(reinterpret_cast<const float4 *>(feat) + off + t + i * G);
+            } else {   // 4 bf16 channels = 8 bytes; widening to fp32 is exact, the sum stays fp32
+                const uint2 u = __ldg(reinterpret_cast<const uint2 *>(feat) + off + t + i * G);
+                const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.x));
+                const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.y));
+                r[i] = make_float4(lo.x, lo.y, hi.x, hi.y);
+            }
+        }
     }
 }
 
@@ -263,7 +273,9 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
     __syncthreads();
     int *table = smem + ((a.V * 12 + 3) & ~3) + warp * T * a.table_stride;
 
-    const float4 *feat4 = reinterpret_cast<const float4 *>(a.feat + b * a.fs_b);
+    const bool fb = a.feat_bf16 != 0;
+    const void *feat4 = fb ? static_cast<const void *>(reinterpret_cast<const __nv_bfloat16 *>(a.feat) + b * a.fs_b)
+                           : static_cast<const void *>(a.feat + b * a.fs_b);
     OutT *vol = reinterpret_cast<OutT *>(a.vol) + b * a.os_b;
     const int g = lane / G;
     const int t = lane % G;
@@ -300,7 +312,7 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
                     if (j >= T) o[u] = -1;
                 }
 #pragma unroll
-                for (int u = 0; u < WIDTH; ++u) gather4<G, CPL>(feat4, o[u], t, ch_ok, r[u]);
+                for (int u = 0; u < WIDTH; ++u) gather4<G, CPL>(feat4, fb, o[u], t, ch_ok, r[u]);
 #pragma unroll
                 for (int u = 0; u < WIDTH; ++u) {
                     const int j = j0 + u * VPI + g;
@@ -329,7 +341,7 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
 #pragma unroll
                     for (int u = 0; u < WIDTH; ++u) {
                         const int o = (k < cnt[u]) ? rows[u * VPI * a.table_stride + k] : -1;
-                        gather4<G, CPL>(feat4, o, t, ch_ok, r[u]);
+                        gather4<G, CPL>(feat4, fb, o, t, ch_ok, r[u]);
                     }
 #pragma unroll
                     for (int u = 0; u < WIDTH; ++u) add4<CPL>(acc[u], r[u]);
@@ -359,7 +371,7 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
 #pragma unroll
                     for (int u = 0; u < DEPTH; ++u) {
                         const int o = (k0 + u < cnt) ? row[k0 + u] : -1;
-                        gather4<G, CPL>(feat4, o, t, ch_ok, r[u]);
+                        gather4<G, CPL>(feat4, fb, o, t, ch_ok, r[u]);
                     }
 #pragma unroll
                     for (int u = 0; u < DEPTH; ++u) add4<CPL>(acc, r[u]);  // ascending view order
@@ -633,7 +645,9 @@ static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 // One launch over at most IVX_MAX_SCENES_PER_LAUNCH scenes.
 static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t stream, bool backward = false) {
-    const bool feat_vec = a.fs_c == 1 && a.C % 4 == 0 && aligned16(a.feat) && a.fs_b % 4 == 0 &&
+    const bool feat_vec = a.fs_c == 1 && a.C % 4 == 0 &&
+                          (a.feat_bf16 ? reinterpret_cast<uintptr_t>(a.feat) % 8 == 0 : aligned16(a.feat)) &&
+                          a.fs_b % 4 == 0 &&
                           a.fs_v % 4 == 0 && a.fs_h % 4 == 0 && a.fs_w % 4 == 0;
     const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
     const bool vol_vec = a.os_c == 1 && a.os_b % 4 == 0 && a.os_n % 4 == 0 &&
@@ -657,6 +671,8 @@ static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t st
             return fail(IVX_ERR_UNSUPPORTED, "feature block of one scene exceeds 2^33 elements");
         a.q_v = (int)(a.fs_v / 4), a.q_h = (int)(a.fs_h / 4), a.q_w = (int)(a.fs_w / 4);
     }
+    if (kernel == nullptr && a.feat_bf16)
+        return fail(IVX_ERR_UNSUPPORTED, "bf16 feature maps need the channels-last layout (C %% 4 == 0, C <= 1024)");
     if (kernel == nullptr) {
         if (vol_dtype != IVX_F32)
             return fail(IVX_ERR_UNSUPPORTED,
@@ -719,12 +735,15 @@ static int backproject_batch(const float *feat, const long long fs[5], int B, in
                              long long proj_stride_b, const float *points, const ivx_grid *grid,
                              const float *new_origin, bool origin_per_scene, int64_t N, void *volume,
                              const int64_t *vs, int vol_dtype, int reduce, uint8_t *valid,
-                             int32_t *count, cudaStream_t stream, bool backward = false) {
+                             int32_t *count, cudaStream_t stream, bool backward = false,
+                             bool feat_bf16 = false) {
     const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
     for (int b0 = 0; b0 < B; b0 += IVX_MAX_SCENES_PER_LAUNCH) {
         const int nb = (B - b0 < IVX_MAX_SCENES_PER_LAUNCH) ? B - b0 : IVX_MAX_SCENES_PER_LAUNCH;
         BpArgs a;
-        a.feat = feat + b0 * fs[0];
+        a.feat = feat_bf16 ? reinterpret_cast<const float *>(reinterpret_cast<const __nv_bfloat16 *>(feat) + b0 * fs[0])
+                           : feat + b0 * fs[0];
+        a.feat_bf16 = feat_bf16 ? 1 : 0;
         a.fs_b = fs[0], a.fs_v = fs[1], a.fs_c = fs[2], a.fs_h = fs[3], a.fs_w = fs[4];
         a.proj = proj + b0 * proj_stride_b;
         a.proj_stride_b = proj_stride_b;
@@ -805,6 +824,30 @@ extern "C" int ivx_backproject_scenes(const float *feat, const int64_t *feat_str
     return backproject_batch(feat, fs, n_scenes, n_views, n_channels, hw, true, proj,
                              12ll * n_views, points, grid, new_origin, true, n_points, volume,
                              vol_strides, vol_dtype, reduce, valid, count, (cudaStream_t)stream);
+}
+
+extern "C" int ivx_backproject_scenes_bf16(const void *feat_bf16, const int64_t *feat_strides, int n_scenes,
+                                           int n_views, int n_channels, const int32_t *hw, const float *proj,
+                                           const float *points, const ivx_grid *grid, const float *new_origin,
+                                           int64_t n_points, void *volume, const int64_t *vol_strides,
+                                           int vol_dtype, int reduce, uint8_t *valid, int32_t *count,
+                                           void *stream) {
+    int rc = validate_grid(points, grid, new_origin, n_points);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE(feat_bf16 && feat_strides && hw && proj && volume && vol_strides, "NULL argument");
+    IVX_REQUIRE(n_scenes > 0 && n_channels > 0, "n_scenes and n_channels must be positive");
+    IVX_REQUIRE(n_views > 0 && n_views <= IVX_MAX_VIEWS, "n_views must be in [1, %d]", IVX_MAX_VIEWS);
+    IVX_REQUIRE(vol_dtype == IVX_F32 || vol_dtype == IVX_BF16, "unknown vol_dtype %d", vol_dtype);
+    IVX_REQUIRE(reduce == IVX_REDUCE_MEAN || reduce == IVX_REDUCE_PARTIAL, "unknown reduce %d", reduce);
+    if (reduce == IVX_REDUCE_PARTIAL)
+        IVX_REQUIRE(count != nullptr && vol_dtype == IVX_F32, "partial sums need count and fp32 volume");
+    for (int b = 0; b < n_scenes; ++b)
+        IVX_REQUIRE(hw[2 * b] > 0 && hw[2 * b + 1] > 0, "scene %d: height/width must be positive", b);
+    const long long fs[5] = {feat_strides[0], feat_strides[1], feat_strides[2], feat_strides[3],
+                             feat_strides[4]};
+    return backproject_batch(static_cast<const float *>(feat_bf16), fs, n_scenes, n_views, n_channels, hw, true,
+                             proj, 12ll * n_views, points, grid, new_origin, true, n_points, volume,
+                             vol_strides, vol_dtype, reduce, valid, count, (cudaStream_t)stream, false, true);
 }
 
 extern "C" int ivx_backproject_scenes_backward(const float *grad_volume, const int64_t *gvol_strides,

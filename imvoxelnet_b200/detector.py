@@ -120,7 +120,10 @@ class ImVoxelNet(_Base):
         projection = torch.stack(projections)
         out_dtype = torch.bfloat16 if self.precision == "bf16" else torch.float32
         # one launch for the whole batch: get_points, backproject, sum / count / mean / mask, stack
-        volume, valids, _ = ops.backproject_scenes(x.float(), hws, projection, self.n_voxels,
+        if not (x.dtype == torch.bfloat16 and self.precision == "bf16" and x.stride(2) == 1
+                and not torch.is_grad_enabled()):
+            x = x.float()       # bf16 maps are consumed as they are in bf16 inference
+        volume, valids, _ = ops.backproject_scenes(x, hws, projection, self.n_voxels,
                                                    self.voxel_size, origins, out_dtype=out_dtype)
         x = self.neck_3d(volume)
         return x, valids, features_2d

@@ -161,7 +161,8 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
     stacked ``(volume [B,C,X,Y,Z], valid [B,1,X,Y,Z] bool, count [B,X,Y,Z]
     int32)``.
 
-    features    [B,V,C,Hf,Wf] fp32 CUDA, any strides (channels-last is fast)
+    features    [B,V,C,Hf,Wf] fp32 CUDA, any strides (channels-last is fast), or
+                channels-last bf16 (half the gather traffic; summed in fp32)
     hw          B pairs ``img_shape // stride`` (:67-68)
     projection  [B,V,3,4] (CPU or CUDA)
     origins     B grid origins (``img_meta['lidar2img']['origin']``); ignored
@@ -195,8 +196,11 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
 
         call.backward = call_backward
         return _BackprojectScenes.apply(feats_cl, call)
-    if features.dtype != torch.float32 or features.dim() != 5:
-        raise TypeError("features must be a float32 [B,V,C,Hf,Wf] tensor")
+    if features.dtype not in (torch.float32, torch.bfloat16) or features.dim() != 5:
+        raise TypeError("features must be a float32 (or channels-last bfloat16) [B,V,C,Hf,Wf] tensor")
+    bf16_maps = features.dtype == torch.bfloat16
+    if bf16_maps and (features.stride(2) != 1 or features.shape[2] % 4):
+        raise TypeError("bfloat16 features must be channels-last with C % 4 == 0")
     b, v, c = features.shape[:3]
     dev = features.device
     xs, ys, zs = (int(t) for t in n_voxels)
@@ -233,7 +237,11 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
     args = (b, v, c, hw_arr, proj.data_ptr(), pp, g, no, n, volume.data_ptr(),
             _lib.i64(volume.stride()), dt, mode, valid.data_ptr(), count.data_ptr())
     with torch.cuda.device(dev):
-        if features.stride(2) != 1 and c % 4 == 0 and repack:
+        if bf16_maps:
+            _lib.check(_lib.lib().ivx_backproject_scenes_bf16(
+                features.data_ptr(), _lib.i64(features.stride()), *args, _stream()),
+                "ivx_backproject_scenes_bf16")
+        elif features.stride(2) != 1 and c % 4 == 0 and repack:
             # the reference's NCHW maps: re-lay them in scratch, then the vectorised kernel
             nbytes = _lib.lib().ivx_backproject_nchw_workspace_bytes(b, v, c, hw_arr)
             workspace = torch.empty(nbytes, dtype=torch.uint8, device=dev)

@@ -131,6 +131,22 @@ IVX_API int ivx_backproject_scenes(const float *feat, const int64_t *feat_stride
                            void *stream);
 
 /*
+ * ivx_backproject_scenes_bf16 -- ivx_backproject_scenes on bf16 feature maps
+ * (channels-last, C % 4 == 0): what a bf16 2D backbone emits.  The reference
+ * keeps fp32 maps (its FPN output, detectors/imvoxelnet.py:50-51); with bf16
+ * maps the gather moves half the bytes.  Values are widened exactly and summed
+ * in fp32, so the result equals ivx_backproject_scenes on the widened maps.
+ */
+IVX_API int ivx_backproject_scenes_bf16(const void *feat_bf16, const int64_t *feat_strides /* host[5] */,
+                                        int n_scenes, int n_views, int n_channels,
+                                        const int32_t *hw /* host[B][2] */, const float *proj,
+                                        const float *points, const ivx_grid *grid,
+                                        const float *new_origin /* host[B][3] */, int64_t n_points,
+                                        void *volume, const int64_t *vol_strides /* host[3] */,
+                                        int vol_dtype, int reduce, uint8_t *valid, int32_t *count,
+                                        void *stream);
+
+/*
  * ivx_backproject_scenes_backward -- gradient of ivx_backproject_scenes with
  * respect to the features: what autograd computes in the reference through
  * the masked gather of detectors/imvoxelnet.py:157 and the view mean of

@@ -381,3 +381,20 @@ def test_gradient_wrt_features_matches_autograd_of_the_reference_ops(name, chann
     assert float(want.abs().max()) > 0
     assert_volume_close(got.numpy(), want.numpy())
     assert_volume_close(vol[0].detach().cpu().numpy(), ref_vol.detach().numpy())
+
+
+@pytest.mark.parametrize("name", ["scannet_fast", "kitti", "nuscenes"])
+def test_bf16_feature_maps_equal_the_widened_maps(name):
+    """bf16 maps are widened exactly and summed in fp32: same result as fp32 maps holding
+    the same (bf16-representable) values -- deep, wide and single-view schedules."""
+    sc, full, origin, P = _scene_inputs(name, seed=41)
+    h, w = sc.feat_hw
+    maps16 = full.to(DEV).to(torch.bfloat16)[None]
+    assert maps16.stride(2) == 1
+    a = ops.backproject_scenes(maps16, [(h, w)], P[None], sc.n_voxels, sc.voxel_size, [origin])
+    b = ops.backproject_scenes(maps16.float(), [(h, w)], P[None], sc.n_voxels, sc.voxel_size, [origin])
+    for u, v in zip(a, b):
+        assert torch.equal(u, v)
+    c = ops.backproject_scenes(maps16, [(h, w)], P[None], sc.n_voxels, sc.voxel_size, [origin],
+                               out_dtype=torch.bfloat16)
+    assert torch.equal(c[0], b[0].to(torch.bfloat16))
