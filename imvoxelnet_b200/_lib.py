@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libivx.so")
 
-IVX_F32, IVX_BF16 = 0, 1
+IVX_F32, IVX_BF16, IVX_U8 = 0, 1, 2
 IVX_REDUCE_MEAN, IVX_REDUCE_PARTIAL = 0, 1
 IVX_MAX_VIEWS = 1024
 
@@ -80,6 +80,12 @@ PROTOTYPES["ivx_conv3d_dgrad_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_
 PROTOTYPES["ivx_conv3d_wgrad_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p]
 PROTOTYPES["ivx_upsample2x_trilinear_backward_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_void_p]
 PROTOTYPES["ivx_upsample2x_trilinear_ndhwc"] = [c_void_p, c_void_p, c_int, c_int, _i32p, c_int, c_void_p]
+PROTOTYPES["ivx_head_split_ndhwc"] = [c_void_p, c_int, c_int, c_int64, c_int, c_int, c_int, c_int, c_void_p,
+                                      c_void_p, c_void_p]
+PROTOTYPES["ivx_resize_mask_trilinear"] = [c_void_p, c_int, c_int, _i32p, _i32p, c_void_p, c_void_p]
+PROTOTYPES["ivx_head_scores"] = [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p,
+                                 c_void_p]
+PROTOTYPES["ivx_compute_projection"] = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]
 RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64, "ivx_conv3d_tc_workspace_bytes": c_int64}
 
 _lib = None

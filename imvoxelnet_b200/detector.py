@@ -16,7 +16,7 @@ from torch import nn
 
 from . import backbone2d, ops
 from . import necks as _necks  # noqa: F401  (importing it registers the four 3D necks)
-from .projection import compute_projection, get_points  # noqa: F401  (get_points is re-exported: heads import it from here, imvoxel_head.py:7)
+from .projection import compute_projection, compute_projection_batch, get_points  # noqa: F401  (get_points is re-exported: heads import it from here, imvoxel_head.py:7)
 from .registry import DETECTORS, HAVE_MMDET, NECKS, build_from, register
 
 if HAVE_MMDET:  # pragma: no cover
@@ -110,14 +110,15 @@ class ImVoxelNet(_Base):
         stride = int(stride)
         x = x.unflatten(0, (batch_size, -1))                     # [B,V,C,Hf,Wf], strides kept
 
-        projections, hws, origins = [], [], []
-        for img_meta in img_metas:
-            # predicted pitch and roll for SUN RGB-D Total at test time (:59-60)
-            angles = features_2d[0] if features_2d is not None and mode == 'test' else None
-            projections.append(compute_projection(img_meta, stride, angles))
-            hws.append((img_meta['img_shape'][0] // stride, img_meta['img_shape'][1] // stride))
-            origins.append(img_meta['lidar2img']['origin'])
-        projection = torch.stack(projections)
+        # predicted pitch and roll for SUN RGB-D Total at test time (:59-60)
+        angles = features_2d[0] if features_2d is not None and mode == 'test' else None
+        hws = [(m['img_shape'][0] // stride, m['img_shape'][1] // stride) for m in img_metas]
+        origins = [m['lidar2img']['origin'] for m in img_metas]
+        n_views = {len(m['lidar2img']['extrinsic']) for m in img_metas}
+        if angles is None and x.is_cuda and len(n_views) == 1:
+            projection = compute_projection_batch(img_metas, stride, x.device)   # one copy + one launch
+        else:
+            projection = torch.stack([compute_projection(m, stride, angles) for m in img_metas])
         out_dtype = torch.bfloat16 if self.precision == "bf16" else torch.float32
         # one launch for the whole batch: get_points, backproject, sum / count / mean / mask, stack
         if not (x.dtype == torch.bfloat16 and self.precision == "bf16" and x.stride(2) == 1

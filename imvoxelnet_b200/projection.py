@@ -8,14 +8,17 @@ Mirrors, by name and argument meaning, the helpers the reference keeps in
 * ``get_points``          <- ``get_points``                     (:132-141)
 * ``grid_new_origin``     <- the ``new_origin`` line            (:139)
 
-These are a few dozen flops per scene and stay on the host with CPU torch
-ops on purpose: they *define the bits* of ``P`` and of the voxel coordinates
-that the CUDA kernel then has to reproduce, so they use the same fp32 torch
-operations, in the same order, as the reference.
+These are a few dozen flops per scene; the host versions use the same fp32
+torch operations, in the same order, as the reference, because they *define
+the bits* of ``P`` and of the voxel coordinates that the CUDA kernel then has
+to reproduce.  ``compute_projection_batch`` is the device version for a whole
+batch (one packed host->device copy and one launch of
+``ivx_compute_projection``, bit-identical to the host loop).
 """
+import numpy as np
 import torch
 
-__all__ = ["compute_projection", "get_extrinsics", "get_points", "grid_new_origin"]
+__all__ = ["compute_projection", "compute_projection_batch", "get_extrinsics", "get_points", "grid_new_origin"]
 
 
 def get_extrinsics(angles):
@@ -63,6 +66,39 @@ def compute_projection(img_meta, stride, angles=None):
     else:
         extrinsics = [torch.tensor(e) for e in lidar2img['extrinsic']]
     return torch.stack([intrinsic @ e[:3] for e in extrinsics])
+
+
+def compute_projection_batch(img_metas, stride, device):
+    """``[B, V, 3, 4]`` CUDA tensor of every scene's matrices, metadata extrinsics only.
+
+    Equals ``torch.stack([compute_projection(m, stride) for m in img_metas]).to(device)`` bit for
+    bit (reference :57-61 with :114-129), without the per-scene CPU tensor ops: the raw
+    intrinsics, ratios and extrinsics travel in one pinned buffer and the products are formed on
+    the device.  All scenes must have the same number of views."""
+    from . import _lib
+    device = torch.device(device)
+    if device.type != "cuda":
+        raise _lib.IvxError("compute_projection_batch needs a CUDA device: use compute_projection on the host")
+    b = len(img_metas)
+    n_views = len(img_metas[0]['lidar2img']['extrinsic'])
+    packed = np.empty(b * 10 + b * n_views * 16, dtype=np.float32)
+    k, r, e = packed[:b * 9].reshape(b, 9), packed[b * 9:b * 10], packed[b * 10:].reshape(b, n_views, 16)
+    for i, meta in enumerate(img_metas):
+        lidar2img = meta['lidar2img']
+        if len(lidar2img['extrinsic']) != n_views:
+            raise ValueError("scenes of one batch must have the same number of views")
+        k[i] = np.asarray(lidar2img['intrinsic'], dtype=np.float32)[:3, :3].reshape(9)
+        r[i] = meta['ori_shape'][0] / (meta['img_shape'][0] / stride)     # double, then one rounding to fp32
+        for v, ext in enumerate(lidar2img['extrinsic']):
+            e[i, v] = np.asarray(ext, dtype=np.float32).reshape(16)
+    host = torch.from_numpy(packed).pin_memory()     # torch's pinned and device caches are stream-ordered
+    with torch.cuda.device(device):
+        dev = host.to(device, non_blocking=True)
+        proj = torch.empty((b, n_views, 3, 4), dtype=torch.float32, device=device)
+        _lib.check(_lib.lib().ivx_compute_projection(
+            dev.data_ptr(), dev.data_ptr() + 4 * b * 9, dev.data_ptr() + 4 * b * 10, b, n_views, proj.data_ptr(),
+            torch.cuda.current_stream().cuda_stream), "ivx_compute_projection")
+    return proj
 
 
 def grid_new_origin(n_voxels, voxel_size, origin):

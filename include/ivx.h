@@ -46,7 +46,7 @@ typedef enum ivx_status {
 } ivx_status;
 
 /* element type of a volume written by the library */
-typedef enum ivx_dtype { IVX_F32 = 0, IVX_BF16 = 1 } ivx_dtype;
+typedef enum ivx_dtype { IVX_F32 = 0, IVX_BF16 = 1, IVX_U8 = 2 /* masks only */ } ivx_dtype;
 
 /* what ivx_backproject_scenes writes */
 typedef enum ivx_reduce {
@@ -421,6 +421,67 @@ IVX_API int ivx_conv3d_wgrad_ndhwc(const ivx_conv3d_params *params, const float 
 IVX_API int ivx_upsample2x_trilinear_backward_ndhwc(const float *grad_y, float *grad_x, int batch,
                                                     int n_channels, const int32_t *in_dims /* host[3] */,
                                                     void *stream);
+
+/* ----------------------- dense-head tail (next row f-2) ----------------------- */
+
+/*
+ * The reference's dense heads (mmdet3d/models/dense_heads/imvoxel_head_v2.py,
+ * imvoxel_head.py) end with three small 3x3x3 convolutions per scale
+ * (centerness 1, box 6 or 7, classes n; _init_layers, imvoxel_head_v2.py:45-49).
+ * The host mirror (imvoxelnet_b200/heads.py) runs those that share an input as
+ * ONE ivx_conv3d_* call with the output channels concatenated (zero-padded to
+ * the kernel's granularity); the entry points below turn that channels-last
+ * result into the tensors the reference returns and prepare its top-k.
+ */
+
+/*
+ * out [batch][c_n][spatial] fp32 = channels [c_off, c_off + c_n) of y [batch][spatial][c_total]
+ * (dtype IVX_F32 or IVX_BF16); the first n_exp channels of the slice become
+ * exp(scale[0] * v) -- torch.exp(scale(reg_final[:, :6])), imvoxel_head_v2.py:306-308, 447;
+ * scale: device pointer to the head's Scale parameter (NULL = 1).
+ */
+IVX_API int ivx_head_split_ndhwc(const void *y, int32_t dtype, int32_t batch, int64_t spatial,
+                                 int32_t c_total, int32_t c_off, int32_t c_n, int32_t n_exp,
+                                 const float *scale, float *out, void *stream);
+
+/*
+ * nn.Upsample(size=out_dims, mode='trilinear')(valid).round().bool()
+ * (imvoxel_head_v2.py:91-93, 224-226; imvoxel_head.py:113-115): mask [batch][X][Y][Z]
+ * with 0/1 entries (mask_dtype IVX_F32, or IVX_U8 for a bool tensor) ->
+ * out [batch][x][y][z] bool.  align_corners = False, source index and weights as
+ * ATen computes them in fp32, round-half-to-even.
+ */
+IVX_API int ivx_resize_mask_trilinear(const void *mask, int32_t mask_dtype, int32_t batch,
+                                      const int32_t in_dims[3] /* host */,
+                                      const int32_t out_dims[3] /* host */, uint8_t *out, void *stream);
+
+/*
+ * scores [batch][spatial][n_classes] = sigmoid(cls) * sigmoid(centerness) * valid and
+ * best [batch][spatial] = max over classes (imvoxel_head_v2.py:262-270), from the
+ * reference-layout tensors centerness [batch][1][spatial], cls [batch][n_classes][spatial],
+ * valid [batch][1][spatial] bool.
+ */
+IVX_API int ivx_head_scores(const float *centerness, const float *cls, const uint8_t *valid, int32_t batch,
+                            int64_t spatial, int32_t n_classes, float *scores, float *best, void *stream);
+
+/* ----------------------- projection set-up on the device (next row f-4) ----------------------- */
+
+/*
+ * ImVoxelNet._compute_projection (detectors/imvoxelnet.py:114-129) for a batch:
+ *   proj[b][v] = K'[b] @ E[b][v][:3],  K'[b] = K[b] with rows 0-1 divided by ratio[b]
+ * with the reference's CPU rounding (fp32 division; products accumulated as
+ * rn(k0*e0) then two fused multiply-adds), so proj is bit-identical to the
+ * tensor the reference builds on the host and copies over (:61).
+ *   intrinsic [B][9]  fp32, the [:3,:3] block of lidar2img['intrinsic'] (:117)
+ *   ratio     [B]     fp32, ori_shape[0] / (img_shape[0] / stride) (:118)
+ *   extrinsic [B][V][16] fp32 row-major 4x4 world->camera matrices (:126)
+ *   proj      [B][V][12] out
+ * All pointers are device memory.  The predicted-angles branch (get_extrinsics,
+ * :121-124, SUN RGB-D Total at test time) stays on the host: its sin/cos bits
+ * are libm's.
+ */
+IVX_API int ivx_compute_projection(const float *intrinsic, const float *ratio, const float *extrinsic,
+                                   int32_t n_scenes, int32_t n_views, float *proj, void *stream);
 
 #ifdef __cplusplus
 }

@@ -91,6 +91,77 @@ def _restore(saved):
 
 
 _cache = {}
+_HEADS = ("mmdet3d/models/dense_heads/imvoxel_head.py", "mmdet3d/models/dense_heads/imvoxel_head_v2.py")
+
+
+def _stub_head_modules(detector_module):
+    """Extra stand-ins the two dense-head files import (mmcv 1.2.7 / mmdet 2.10.0 names)."""
+    import torch
+
+    mods = {}
+
+    def new(name):
+        mods[name] = types.ModuleType(name)
+        return mods[name]
+
+    core = new("mmdet.core")
+
+    def multi_apply(func, *args, **kwargs):         # mmdet/core/utils/misc.py: map + transpose
+        from functools import partial
+        results = map(partial(func, **kwargs) if kwargs else func, *args)
+        return tuple(map(list, zip(*results)))
+
+    core.multi_apply = multi_apply
+    core.reduce_mean = lambda t: t
+    builder = new("mmdet.models.builder")
+    builder.HEADS = _Registry()
+    builder.build_loss = lambda cfg: None
+    cnn = new("mmcv.cnn")
+
+    class Scale(torch.nn.Module):                   # mmcv/cnn/bricks/scale.py: learnable scalar factor
+        def __init__(self, scale=1.0):
+            super().__init__()
+            self.scale = torch.nn.Parameter(torch.tensor(scale, dtype=torch.float))
+
+        def forward(self, x):
+            return x * self.scale
+
+    cnn.Scale = Scale
+    cnn.bias_init_with_prob = lambda p: 0.0
+    cnn.normal_init = lambda *a, **k: None
+    det = new("mmdet3d.models.detectors.imvoxelnet")
+    det.get_points = detector_module.get_points
+    new("mmdet3d.models"), new("mmdet3d.models.detectors"), new("mmdet3d.core.bbox")
+    structures = new("mmdet3d.core.bbox.structures")
+    structures.rotation_3d_in_axis = None
+    post = new("mmdet3d.core.post_processing")
+    post.aligned_3d_nms = post.box3d_multiclass_nms = None
+    return mods
+
+
+def load_heads():
+    """Return ``(imvoxel_head module, imvoxel_head_v2 module)`` of the live reference."""
+    if "heads" in _cache:
+        return _cache["heads"]
+    detector_module, _ = load()
+    saved = _stub_modules()
+    extra = _stub_head_modules(detector_module)
+    for name, mod in extra.items():
+        saved.setdefault(name, sys.modules.get(name))
+        sys.modules[name] = mod
+    try:
+        out = []
+        for i, rel in enumerate(_HEADS):
+            spec = importlib.util.spec_from_file_location(
+                f"_ivx_reference_head_{i}", os.path.join(REFERENCE_ROOT, rel))
+            mod = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(mod)
+            out.append(mod)
+    finally:
+        _restore(saved)
+    _cache["heads"] = tuple(out)
+    return _cache["heads"]
+
 
 
 def load():

@@ -173,7 +173,7 @@ def main():
     np.savez(os.path.join(HERE, "fullsize_digests.npz"), **dig)
 
 
-if __name__ == "__main__" and "--necks" not in sys.argv:
+if __name__ == "__main__" and not {"--necks", "--heads"} & set(sys.argv):
     main()
 
 
@@ -203,3 +203,49 @@ def make_necks():
 
 if __name__ == "__main__" and "--necks" in sys.argv:
     make_necks()
+
+
+# --------------------------------------------------------------------------
+# dense heads: the reference classes' forward(), the valid-mask resampling and
+# the pre-NMS scores (imvoxel_head_v2.py:91-93, 262-270), small sizes
+# --------------------------------------------------------------------------
+from tests.golden.cases import HEAD_CASES, MASK_CASES  # noqa: E402
+
+
+def make_heads():
+    from oracle import torch_heads
+    v1, v2 = ref_loader.load_heads()
+    for i, (name, (kw, _, shapes)) in enumerate(HEAD_CASES.items()):
+        torch.manual_seed(300 + i)
+        head = getattr(v2 if name.endswith("V2") else v1, name)(**kw).eval()
+        torch_heads.randomise(head, seed=400 + i)
+        xs = [torch.randn(s) for s in shapes]
+        with torch.no_grad():
+            centernesses, bbox_preds, cls_scores = head(xs)
+        blob = {f"sd/{k}": v.numpy() for k, v in head.state_dict().items()}
+        for j, x in enumerate(xs):
+            blob[f"x{j}"] = x.numpy()
+            blob[f"centerness{j}"] = centernesses[j].numpy()
+            blob[f"bbox{j}"] = bbox_preds[j].numpy()
+            blob[f"cls{j}"] = cls_scores[j].numpy()
+        # scores of scene 0, level 0, exactly the statements of _get_bboxes_single (:262-270)
+        valid = torch.rand(shapes[0][2:], generator=torch.Generator().manual_seed(i))[None] > 0.3
+        n_classes = kw["n_classes"]
+        centerness = centernesses[0][0].permute(1, 2, 3, 0).reshape(-1).sigmoid()
+        scores = cls_scores[0][0].permute(1, 2, 3, 0).reshape(-1, n_classes).sigmoid()
+        scores = scores * centerness[:, None] * valid.permute(1, 2, 3, 0).reshape(-1)[:, None]
+        max_scores, _ = scores.max(dim=1)
+        blob["score_valid"], blob["scores"], blob["max_scores"] = valid.numpy(), scores.numpy(), max_scores.numpy()
+        np.savez_compressed(os.path.join(HERE, f"head_{name}.npz"), **blob)
+        print(name, [tuple(o.shape) for o in bbox_preds])
+    for i, (name, (shape, sizes)) in enumerate(MASK_CASES.items()):
+        valid = (torch.rand(shape, generator=torch.Generator().manual_seed(500 + i)) > 0.45).float()
+        blob = {"valid": valid.numpy().astype(np.bool_)}
+        for j, size in enumerate(sizes):   # the reference's statement, imvoxel_head_v2.py:93
+            blob[f"out{j}"] = torch.nn.Upsample(size=size, mode='trilinear')(valid).round().bool().numpy()
+        np.savez_compressed(os.path.join(HERE, f"mask_{name}.npz"), **blob)
+        print(name, [int(blob[f"out{j}"].sum()) for j in range(len(sizes))])
+
+
+if __name__ == "__main__" and "--heads" in sys.argv:
+    make_heads()
