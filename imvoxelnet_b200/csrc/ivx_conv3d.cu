@@ -241,6 +241,134 @@ __global__ void __launch_bounds__(256) upsample2x_trilinear_kernel(
     }
 }
 
+
+// Same operation, one thread per INPUT voxel and 16 bytes of channels (8 bf16 / 4 fp32): the eight
+// outputs (2i + d) of a voxel all read its 3x3x3 neighbourhood, so the 27 vector loads and the
+// z- and y-interpolations are shared between them (the per-output kernel above does 64 loads for
+// the same work).  Output o = 2i + d has source index i - 0.25 (d = 0) or i + 0.25 (d = 1):
+//   d = 0: 0.25 * in[i-1] + 0.75 * in[i]      (i = 0: ATen clamps the index to 0: 1 * in[0] + 0 * in[1])
+//   d = 1: 0.75 * in[i]   + 0.25 * in[min(i+1, n-1)]
+// evaluated with the same products and sums, in the same z, y, x order, as the kernel above.
+template <int N>
+struct ChanVec {
+    float v[N];
+};
+
+template <typename T>
+struct UpVec;
+template <>
+struct UpVec<float> {
+    static constexpr int N = 4;
+    __device__ static ChanVec<4> load(const float *p) {
+        const float4 f = __ldg(reinterpret_cast<const float4 *>(p));
+        return {{f.x, f.y, f.z, f.w}};
+    }
+    __device__ static void store(float *p, const ChanVec<4> &c) {
+        __stcs(reinterpret_cast<float4 *>(p), make_float4(c.v[0], c.v[1], c.v[2], c.v[3]));
+    }
+};
+template <>
+struct UpVec<__nv_bfloat16> {
+    static constexpr int N = 8;
+    __device__ static ChanVec<8> load(const __nv_bfloat16 *p) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4 *>(p));
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u);
+        ChanVec<8> c;
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            const float2 f = __bfloat1622float2(h[e]);
+            c.v[2 * e] = f.x, c.v[2 * e + 1] = f.y;
+        }
+        return c;
+    }
+    __device__ static void store(__nv_bfloat16 *p, const ChanVec<8> &c) {
+        uint4 u;
+        __nv_bfloat162 *h = reinterpret_cast<__nv_bfloat162 *>(&u);
+#pragma unroll
+        for (int e = 0; e < 4; ++e) h[e] = __floats2bfloat162_rn(c.v[2 * e], c.v[2 * e + 1]);
+        __stcs(reinterpret_cast<uint4 *>(p), u);
+    }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(128) upsample2x_trilinear_voxel_kernel(
+    const T *__restrict__ x, T *__restrict__ y, int B, int X, int Y, int Z, int CV) {
+    constexpr int N = UpVec<T>::N;
+    using V = ChanVec<N>;
+    const long long total = (long long)B * X * Y * Z * CV;
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i >= total) return;
+    const int cv = (int)(i % CV);
+    long long t = i / CV;
+    const int zi = (int)(t % Z);
+    t /= Z;
+    const int yi = (int)(t % Y);
+    t /= Y;
+    const int xi = (int)(t % X);
+    const int b = (int)(t / X);
+    // neighbourhood positions {i-1, i, i+1} (clamped) per axis and, per output parity d, which two of
+    // them are combined with which weights
+    const int xs[3] = {max(xi - 1, 0), xi, min(xi + 1, X - 1)};
+    const int ys[3] = {max(yi - 1, 0), yi, min(yi + 1, Y - 1)};
+    const int zs[3] = {max(zi - 1, 0), zi, min(zi + 1, Z - 1)};
+    // lo: combine positions (0, 1), else (1, 2)
+    auto taps = [](int idx, int d, bool &lo, float &wa, float &wb) {
+        if (d == 1) lo = false, wa = 0.75f, wb = 0.25f;
+        else if (idx > 0) lo = true, wa = 0.25f, wb = 0.75f;
+        else lo = false, wa = 1.f, wb = 0.f;
+    };
+    // w0 * (lo ? p0 : p1) + w1 * (lo ? p1 : p2), selected element-wise so everything stays in registers
+    auto lerp3 = [](const V &p0, const V &p1, const V &p2, bool lo, float w0, float w1) {
+        V r;
+#pragma unroll
+        for (int e = 0; e < N; ++e) r.v[e] = w0 * (lo ? p0.v[e] : p1.v[e]) + w1 * (lo ? p1.v[e] : p2.v[e]);
+        return r;
+    };
+    const long long cstride = (long long)CV * N;
+    V yz[3][2][2];   // [x position][dy][dz]: interpolated along z, then y
+#pragma unroll
+    for (int px = 0; px < 3; ++px) {
+        V zl[3][2];  // [y position][dz]
+#pragma unroll
+        for (int py = 0; py < 3; ++py) {
+            const T *col = x + ((((long long)b * X + xs[px]) * Y + ys[py]) * Z) * cstride + (long long)cv * N;
+            V in[3];
+#pragma unroll
+            for (int pz = 0; pz < 3; ++pz) in[pz] = UpVec<T>::load(col + zs[pz] * cstride);
+#pragma unroll
+            for (int dz = 0; dz < 2; ++dz) {
+                bool lo;
+                float wa, wb;
+                taps(zi, dz, lo, wa, wb);
+                zl[py][dz] = lerp3(in[0], in[1], in[2], lo, wa, wb);
+            }
+        }
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy) {
+            bool lo;
+            float wa, wb;
+            taps(yi, dy, lo, wa, wb);
+#pragma unroll
+            for (int dz = 0; dz < 2; ++dz) yz[px][dy][dz] = lerp3(zl[0][dz], zl[1][dz], zl[2][dz], lo, wa, wb);
+        }
+    }
+#pragma unroll
+    for (int dx = 0; dx < 2; ++dx) {
+        bool lo;
+        float wa, wb;
+        taps(xi, dx, lo, wa, wb);
+#pragma unroll
+        for (int dy = 0; dy < 2; ++dy)
+#pragma unroll
+            for (int dz = 0; dz < 2; ++dz) {
+                const V r = lerp3(yz[0][dy][dz], yz[1][dy][dz], yz[2][dy][dz], lo, wa, wb);
+                const long long ovox = (((long long)b * (2 * X) + 2 * xi + dx) * (2 * Y) + 2 * yi + dy) * (2 * Z) +
+                                       2 * zi + dz;
+                UpVec<T>::store(y + ovox * cstride + (long long)cv * N, r);
+            }
+    }
+}
+
 }  // namespace ivx
 
 using namespace ivx;
@@ -307,10 +435,26 @@ extern "C" int ivx_upsample2x_trilinear_ndhwc(const void *x, void *y, int batch,
     IVX_REQUIRE(batch > 0 && n_channels > 0 && n_channels % 4 == 0, "channels must be a multiple of 4");
     IVX_REQUIRE(in_dims[0] > 0 && in_dims[1] > 0 && in_dims[2] > 0, "bad dims");
     IVX_REQUIRE(dtype == IVX_F32 || dtype == IVX_BF16, "unknown dtype");
-    const long long total = 8ll * batch * in_dims[0] * in_dims[1] * in_dims[2] * (n_channels / 4);
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long voxels = (long long)batch * in_dims[0] * in_dims[1] * in_dims[2];
+    const int per_thread = dtype == IVX_F32 ? 4 : 8;          // channels in 16 bytes
+    if (n_channels % per_thread == 0 && (reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) % 16 == 0) {
+        const int cv = n_channels / per_thread;
+        const long long blocks = (voxels * cv + 127) / 128;
+        IVX_REQUIRE(blocks < (1ll << 31), "too many voxels");
+        if (dtype == IVX_F32)
+            upsample2x_trilinear_voxel_kernel<float><<<(unsigned)blocks, 128, 0, s>>>(
+                static_cast<const float *>(x), static_cast<float *>(y), batch, in_dims[0], in_dims[1], in_dims[2], cv);
+        else
+            upsample2x_trilinear_voxel_kernel<__nv_bfloat16><<<(unsigned)blocks, 128, 0, s>>>(
+                static_cast<const __nv_bfloat16 *>(x), static_cast<__nv_bfloat16 *>(y), batch, in_dims[0],
+                in_dims[1], in_dims[2], cv);
+        IVX_CHECK_LAUNCH("upsample launch");
+        return IVX_OK;
+    }
+    const long long total = 8ll * voxels * (n_channels / 4);
     long long gx = (total + 255) / 256;
     if (gx > kNumSMs * 32) gx = kNumSMs * 32;
-    cudaStream_t s = (cudaStream_t)stream;
     if (dtype == IVX_F32)
         upsample2x_trilinear_kernel<float><<<(unsigned)gx, 256, 0, s>>>(
             static_cast<const float *>(x), static_cast<float *>(y), batch, in_dims[0], in_dims[1],

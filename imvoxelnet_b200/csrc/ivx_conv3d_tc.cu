@@ -15,17 +15,25 @@
 //   * one 2-D TMA load of the [n][64] weight slice, same layout.
 // A single thread issues tcgen05.mma (M=128, N=c_out tile, K=16, bf16 in, fp32
 // accumulate in TMEM); tcgen05.commit releases the smem stage and, after the
-// last k-step, hands the accumulator to the four epilogue warps, which read
-// it with tcgen05.ld, apply folded BN scale/shift, residual, ReLU, convert to
-// bf16, stage 64-channel slabs in swizzled shared memory and TMA-store them
-// (the store clips partial tiles).  Two accumulators in TMEM (2 x N columns)
-// let the epilogue of tile i overlap the main loop of tile i+1; CTAs are
-// persistent over tiles.
+// last k-step, hands the accumulator to the eight epilogue warps (two per TMEM
+// lane quarter, 32 of a slab's 64 channels each), which read it with
+// tcgen05.ld, apply folded BN scale/shift, residual, ReLU, convert to bf16,
+// stage 64-channel slabs in swizzled shared memory and TMA-store them (the
+// store clips partial tiles).  Where shared memory allows, the residual tile is
+// TMA-loaded into a slab n_slabs - 1 chunks ahead (3 to 8 slabs rotate), so
+// adding it is a read-modify-write of shared memory instead of an exposed
+// global load: layers with few k-steps (1x1x1, transposed) are bound by this
+// epilogue and by the latency of that load.
+// Two accumulators in TMEM (2 x N columns) let the epilogue of tile i overlap
+// the main loop of tile i+1; CTAs are persistent over tiles.
+#include <type_traits>
+
 #include "ivx_tc_ptx.cuh"
 
 namespace ivx {
 
-constexpr int TC_THREADS = 192;      // warp 0: TMA, warp 1: MMA, warps 2..5: epilogue
+constexpr int TC_THREADS = 320;      // warp 0: TMA, warp 1: MMA, warps 2..9: epilogue
+constexpr int TC_EPI_WARPS = 8;
 constexpr int TC_ROWS = 128;         // UMMA M
 constexpr int TC_KCHUNK = 64;        // bf16 channels per k-step = one 128B swizzle row
 constexpr int TC_A_BYTES = TC_ROWS * 128;
@@ -38,12 +46,15 @@ struct TcArgs {
     int out_dims[3], batch;
     int box[3];                 // output voxels per tile along x, y, z
     int tiles[3];               // tiles along x, y, z
-    long long n_tiles;          // batch * tiles * n_splits
+    long long n_tiles;          // batch * tiles * n_splits * k_splits (< 2^31)
+    TileDiv div_k, div_n, div_z, div_y, div_x;   // tile index -> (split, n-tile, z, y, x, batch)
     int stages;
     int relu, residual_after_act;
     float post_scale;
     const float *scale, *shift;
     const __nv_bfloat16 *res;
+    int n_slabs;                // output staging slabs: 2, or 3..8 when the residual comes in by TMA
+    int res_tma;                // residual tiles are TMA-loaded into the slabs (needs n_slabs >= 3)
     // transposed layers (ConvTranspose3d, kernel == stride): rows are INPUT voxels, the GEMM
     // columns are (tap, c_out); every n-tile lies inside one tap and is stored with that
     // tap's offset through an output map whose element strides are the layer stride
@@ -63,34 +74,74 @@ struct TileCoord {
     int b, x0, y0, z0, n0;
 };
 
-__device__ __forceinline__ TileCoord decode_tile(const TcArgs &a, long long t) {
+__device__ __forceinline__ TileCoord decode_tile(const TcArgs &a, long long tile) {
     TileCoord c;
-    t /= a.k_splits;            // the split index is the fastest: CTAs of one tile run together
-    c.n0 = (int)(t % a.n_splits) * a.n_tile;
-    t /= a.n_splits;
-    c.z0 = (int)(t % a.tiles[2]) * a.box[2];
-    t /= a.tiles[2];
-    c.y0 = (int)(t % a.tiles[1]) * a.box[1];
-    t /= a.tiles[1];
-    c.x0 = (int)(t % a.tiles[0]) * a.box[0];
-    c.b = (int)(t / a.tiles[0]);
+    int t = a.div_k.div((int)tile);   // the split index is the fastest: CTAs of one tile run together
+    int r;
+    t = a.div_n.divmod(t, r);
+    c.n0 = r * a.n_tile;
+    t = a.div_z.divmod(t, r);
+    c.z0 = r * a.box[2];
+    t = a.div_y.divmod(t, r);
+    c.y0 = r * a.box[1];
+    c.b = a.div_x.divmod(t, r);
+    c.x0 = r * a.box[0];
     return c;
+}
+
+// One 8-channel group of the fused epilogue: y = post * (max(z * sc + sh [+ r], floor) [+ r]).
+// RES: 0 no residual, 1 residual before the activation, 2 after it.
+template <int RES, bool POST>
+__device__ __forceinline__ uint4 epilogue8(const uint32_t *v, uint32_t ss_addr, uint4 res, float act_floor,
+                                           float post_scale) {
+    float f[8];
+#pragma unroll
+    for (int e = 0; e < 8; e += 2) {   // (scale, shift) of two channels per 16-byte shared-memory read
+        const uint4 ss = lds128(ss_addr + (uint32_t)e * 8);
+        f[e] = fmaf(__uint_as_float(v[e]), __uint_as_float(ss.x), __uint_as_float(ss.y));
+        f[e + 1] = fmaf(__uint_as_float(v[e + 1]), __uint_as_float(ss.z), __uint_as_float(ss.w));
+    }
+    float r[8];
+    if (RES != 0) {
+        const uint32_t w[4] = {res.x, res.y, res.z, res.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {   // bf16 -> fp32 is a 16-bit shift
+            r[2 * e] = __uint_as_float(w[e] << 16);
+            r[2 * e + 1] = __uint_as_float(w[e] & 0xffff0000u);
+        }
+    }
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+        if (RES == 1) f[e] += r[e];
+        f[e] = fmaxf(f[e], act_floor);
+        if (RES == 2) f[e] += r[e];
+        if (POST) f[e] *= post_scale;
+    }
+    uint4 o;
+    __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
+    __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
+    o.x = *reinterpret_cast<uint32_t *>(&b0), o.y = *reinterpret_cast<uint32_t *>(&b1);
+    o.z = *reinterpret_cast<uint32_t *>(&b2), o.w = *reinterpret_cast<uint32_t *>(&b3);
+    return o;
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
-                 const __grid_constant__ CUtensorMap map_y, const __grid_constant__ TcArgs a) {
+                 const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_r,
+                 const __grid_constant__ TcArgs a) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // carve-up (all tiles 1024-byte aligned for the 128B swizzle)
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int b_bytes = a.n_tile * 128;
     const int stage_bytes = TC_A_BYTES + b_bytes;
     uint8_t *stage_base = smem;
-    uint8_t *slab_base = smem + (size_t)a.stages * stage_bytes;  // 2 output slabs of 128 x 128 B
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + 2 * TC_A_BYTES);
+    uint8_t *slab_base = smem + (size_t)a.stages * stage_bytes;  // n_slabs output slabs of 128 x 128 B
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + (size_t)a.n_slabs * TC_A_BYTES);
     uint64_t *full_bar = bars, *empty_bar = bars + a.stages;
     uint64_t *acc_full = bars + 2 * a.stages, *acc_empty = acc_full + 2;
-    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
+    uint64_t *res_bar = acc_empty + 2;               // residual tile landed in slab s (up to 8 slabs)
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(res_bar + 8);
+    float2 *ss_buf = reinterpret_cast<float2 *>(reinterpret_cast<uint8_t *>(bars) + 512);   // 64 x (scale, shift)
     volatile uint32_t *split_flag = tmem_slot + 1;   // "this CTA finishes the tile" (split-K)
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -103,12 +154,14 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(smem_u32(acc_full + i), 1);
-            mbar_init(smem_u32(acc_empty + i), 4);  // one arrive per epilogue warp
+            mbar_init(smem_u32(acc_empty + i), TC_EPI_WARPS);  // one arrive per epilogue warp
         }
+        for (int i = 0; i < 8; ++i) mbar_init(smem_u32(res_bar + i), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_w) : "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_y) : "memory");
+        if (a.res_tma) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_r) : "memory");
     }
     if (warp == 1) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -173,14 +226,36 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             }
         }
     } else {
-        // ------------------------------ epilogue (4 warps) ------------------------------
+        // ------------------------------ epilogue (8 warps) ------------------------------
         const int q = warp & 3;             // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;   // which 32 of a slab's 64 channels this warp handles
         const int row = q * 32 + lane;      // tile row = accumulator lane
         const int box_rows = a.box[0] * a.box[1] * a.box[2];
         const int iz = row % a.box[2], iy = (row / a.box[2]) % a.box[1], ix = row / (a.box[2] * a.box[1]);
         const bool epi_leader = (warp == 2 && lane == 0);
-        uint32_t acc = 0, acc_phase = 0;
+        const int epi_tid = threadIdx.x - 64;
+        const uint32_t ss_addr = smem_u32(ss_buf);
+        // y = post * (max(z [+ r], floor) [+ r]): residual before or after the activation
+        const int epi_mode = (a.res ? (a.residual_after_act ? 2 : 1) : 0) + (a.post_scale != 1.f ? 3 : 0);
+        const float act_floor = a.relu ? 0.f : -INFINITY;
+        uint32_t acc = 0, acc_phase = 0, res_phase = 0;   // res_phase: bit s = parity of res_bar[s]
         int slab = 0;
+        // residual by TMA: chunk i (64 channels of a tile) is staged in slab i % n_slabs; its residual
+        // is requested n_slabs - 1 chunks ahead, as soon as the store that last read that slab has drained
+        const int chunks_per_tile = a.n_tile / 64;
+        long long chunk_i = 0;
+        auto request_residual = [&](long long ci) {       // leader only
+            const long long t2 = blockIdx.x + (ci / chunks_per_tile) * (long long)gridDim.x;
+            if (t2 >= a.n_tiles) return;
+            const TileCoord c2 = decode_tile(a, t2);
+            const int into = (int)(ci % a.n_slabs);
+            const uint32_t bar = smem_u32(res_bar + into);
+            mbar_expect_tx(bar, (uint32_t)(box_rows * 128));
+            tma_load_5d(smem_u32(slab_base + (size_t)into * TC_A_BYTES), &map_r, bar,
+                        c2.n0 + (int)(ci % chunks_per_tile) * 64, c2.z0, c2.y0, c2.x0, c2.b);
+        };
+        if (a.res_tma && epi_leader)
+            for (int ci = 0; ci < a.n_slabs - 1; ++ci) request_residual(ci);
         for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
             const TileCoord tc = decode_tile(a, t);
             const int tap_t = a.transposed ? tc.n0 / a.c_out : 0;   // which (kx,ky,kz) this n-tile is
@@ -196,7 +271,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 // phase A (every CTA of the tile): add the partial accumulator into the workspace
                 const long long out_tile = t / a.k_splits;
                 ws_row = a.ws + (out_tile * TC_ROWS + row) * a.n_tile;
-                for (int c = 0; c < a.n_tile; c += 32) {
+                for (int c = half * 32; c < a.n_tile; c += 64) {
                     uint32_t v[32];
                     tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c, v);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
@@ -212,19 +287,30 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 if (lane == 0) mbar_arrive(smem_u32(acc_empty + acc));
                 if (++acc == 2) acc = 0, acc_phase ^= 1;
                 __threadfence();
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (epi_leader) *split_flag = atomicAdd(a.counters + out_tile, 1u) == (unsigned)(a.k_splits - 1);
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (!*split_flag) continue;   // another CTA finishes this tile
                 __threadfence();              // phase B (last CTA): all partials are visible
             }
             for (int c0 = 0; c0 < a.n_tile; c0 += 64) {
-                const int ncols = a.n_tile - c0 < 64 ? a.n_tile - c0 : 64;
                 uint8_t *slab_ptr = slab_base + slab * TC_A_BYTES;
-                // the TMA store that last read this slab must be done before we overwrite it
-                if (epi_leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-                for (int h = 0; h < ncols; h += 32) {
+                // (scale, shift) of this chunk's 64 channels -> shared memory (everyone is past the
+                // previous chunk's barrier, so nobody still reads the old ones)
+                if (epi_tid < 64) {
+                    const int c = ch0 + c0 + epi_tid;
+                    ss_buf[epi_tid] = make_float2(a.scale ? __ldg(a.scale + c) : 1.f, a.shift ? __ldg(a.shift + c) : 0.f);
+                }
+                // the TMA store that last read this slab must be done before we overwrite it (with the
+                // residual by TMA that was checked before its load was issued)
+                if (!a.res_tma && epi_leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (a.res_tma) {   // the residual of this chunk has landed in the slab
+                    mbar_wait(smem_u32(res_bar + slab), (res_phase >> slab) & 1u);
+                    res_phase ^= 1u << slab;
+                }
+                {
+                    const int h = half * 32;
                     uint32_t v[32];
                     if (ws_row == nullptr) {
                         tmem_ld32(tmem_base + acc * acc_stride + ((uint32_t)(q * 32) << 16) + c0 + h, v);
@@ -240,43 +326,35 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                         }
                     }
                     const int ch = ch0 + c0 + h;
+                    const uint32_t row_addr = smem_u32(slab_ptr) + row * 128;
+                    auto run = [&](auto res_c, auto post_c) {
+                        constexpr int RES = decltype(res_c)::value;
+                        constexpr bool POST = decltype(post_c)::value;
 #pragma unroll
-                    for (int j = 0; j < 32; j += 8) {
-                        float f[8];
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            const float sc = a.scale ? __ldg(a.scale + ch + j + e) : 1.f;
-                            const float sh = a.shift ? __ldg(a.shift + ch + j + e) : 0.f;
-                            f[e] = fmaf(__uint_as_float(v[j + e]), sc, sh);
-                        }
-                        float r[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                        if (a.res && row_ok) {
-                            const uint4 u = __ldg(reinterpret_cast<const uint4 *>(a.res + ovox * a.c_out + ch + j));
-                            const __nv_bfloat162 *p2 = reinterpret_cast<const __nv_bfloat162 *>(&u);
-#pragma unroll
-                            for (int e = 0; e < 4; ++e) {
-                                const float2 fr = __bfloat1622float2(p2[e]);
-                                r[2 * e] = fr.x, r[2 * e + 1] = fr.y;
+                        for (int j = 0; j < 32; j += 8) {
+                            const int chunk = (h + j) >> 3;  // 16-byte chunk inside the 128-byte row
+                            const uint32_t cell = row_addr + ((chunk ^ (row & 7)) << 4);
+                            uint4 u = make_uint4(0u, 0u, 0u, 0u);
+                            if (RES != 0) {
+                                if (a.res_tma) u = lds128(cell);
+                                else if (row_ok) u = __ldg(reinterpret_cast<const uint4 *>(a.res + ovox * a.c_out + ch + j));
                             }
+                            sts128(cell, epilogue8<RES, POST>(v + j, ss_addr + (uint32_t)(h + j) * 8, u, act_floor,
+                                                              a.post_scale));
                         }
-#pragma unroll
-                        for (int e = 0; e < 8; ++e) {
-                            if (a.res && !a.residual_after_act) f[e] += r[e];
-                            if (a.relu) f[e] = fmaxf(f[e], 0.f);
-                            if (a.res && a.residual_after_act) f[e] += r[e];
-                            f[e] *= a.post_scale;
-                        }
-                        uint4 o;
-                        __nv_bfloat162 b0 = __floats2bfloat162_rn(f[0], f[1]), b1 = __floats2bfloat162_rn(f[2], f[3]);
-                        __nv_bfloat162 b2 = __floats2bfloat162_rn(f[4], f[5]), b3 = __floats2bfloat162_rn(f[6], f[7]);
-                        o.x = *reinterpret_cast<uint32_t *>(&b0), o.y = *reinterpret_cast<uint32_t *>(&b1);
-                        o.z = *reinterpret_cast<uint32_t *>(&b2), o.w = *reinterpret_cast<uint32_t *>(&b3);
-                        const int chunk = (h + j) >> 3;  // 16-byte chunk inside the 128-byte row
-                        *reinterpret_cast<uint4 *>(slab_ptr + row * 128 + ((chunk ^ (row & 7)) << 4)) = o;
+                    };
+                    using std::integral_constant;
+                    switch (epi_mode) {
+                        case 0: run(integral_constant<int, 0>{}, integral_constant<bool, false>{}); break;
+                        case 1: run(integral_constant<int, 1>{}, integral_constant<bool, false>{}); break;
+                        case 2: run(integral_constant<int, 2>{}, integral_constant<bool, false>{}); break;
+                        case 3: run(integral_constant<int, 0>{}, integral_constant<bool, true>{}); break;
+                        case 4: run(integral_constant<int, 1>{}, integral_constant<bool, true>{}); break;
+                        default: run(integral_constant<int, 2>{}, integral_constant<bool, true>{}); break;
                     }
                 }
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // st.shared -> visible to TMA
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (epi_leader) {
                     if (a.transposed)
                         tma_store_5d(&map_y, smem_u32(slab_ptr), ch0 + c0, tc.z0 * a.up[2] + tkz,
@@ -284,8 +362,13 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     else
                         tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.z0, tc.y0, tc.x0, tc.b);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+                    if (a.res_tma) {   // once the store of the previous chunk has drained, its slab takes a new chunk
+                        asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                        request_residual(chunk_i + a.n_slabs - 1);
+                    }
                 }
-                slab ^= 1;
+                ++chunk_i;
+                if (++slab == a.n_slabs) slab = 0;
             }
             if (ws_row != nullptr) {
                 if (epi_leader) a.counters[t / a.k_splits] = 0;   // ready for the next launch
@@ -435,6 +518,8 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
         }
     }
     a.n_tiles = out_tiles * a.k_splits;
+    a.div_k = make_tilediv(a.k_splits), a.div_n = make_tilediv(a.n_splits);
+    a.div_z = make_tilediv(a.tiles[2]), a.div_y = make_tilediv(a.tiles[1]), a.div_x = make_tilediv(a.tiles[0]);
 }
 
 extern "C" int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *p) {
@@ -478,6 +563,7 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         } else {   // no (or too small a) workspace: one CTA per tile, still correct
             a.n_tiles = out_tiles;
             a.k_splits = 1;
+            a.div_k = make_tilediv(1);
             a.steps_per_split = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
         }
     }
@@ -489,13 +575,32 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
     const int n_total = p->c_out * up_taps;
 
     const int stage_bytes = TC_A_BYTES + a.n_tile * 128;
-    const int fixed = 2 * TC_A_BYTES + 1024 /* barriers */ + 1024 /* alignment slack */;
-    a.stages = (227 * 1024 - fixed) / stage_bytes;
-    if (a.stages > 8) a.stages = 8;
+    const int k_steps_total = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
+    const int budget = 227 * 1024 - 1024 /* barriers */ - 1024 /* alignment slack */;
+    auto stages_with = [&](int n_slabs) {
+        const int st = (budget - n_slabs * TC_A_BYTES) / stage_bytes;
+        return st > 8 ? 8 : st;
+    };
+    // residual through TMA needs extra slabs.  A layer with few k-steps is bound by the epilogue and by
+    // the latency of the residual load, not by the main loop: give it a short pipeline and up to 8
+    // slabs (residual requested 7 chunks ahead).  Otherwise one extra slab, if 4 stages remain.
+    a.n_slabs = 2, a.res_tma = 0;
+    if (residual != nullptr && a.k_splits == 1 && !p->transposed) {
+        if (k_steps_total <= 16) {
+            for (int st = 4; st >= 2 && !a.res_tma; --st) {
+                int slabs = (budget - st * stage_bytes) / TC_A_BYTES;
+                if (slabs > 8) slabs = 8;
+                if (slabs >= 4) a.n_slabs = slabs, a.res_tma = 1;
+            }
+        } else if (stages_with(3) >= 4) {
+            a.n_slabs = 3, a.res_tma = 1;
+        }
+    }
+    a.stages = stages_with(a.n_slabs);
     IVX_REQUIRE(a.stages >= 2, "not enough shared memory for a 2-stage pipeline");
-    const size_t smem = (size_t)a.stages * stage_bytes + fixed;
+    const size_t smem = (size_t)a.stages * stage_bytes + a.n_slabs * TC_A_BYTES + 2048;
 
-    alignas(64) CUtensorMap map_x, map_w, map_y;
+    alignas(64) CUtensorMap map_x, map_w, map_y, map_r;
     {
         const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[2], (cuuint64_t)p->in_dims[1],
                                     (cuuint64_t)p->in_dims[0], (cuuint64_t)p->batch};
@@ -533,6 +638,11 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
         const cuuint32_t es[5] = {1, (cuuint32_t)a.up[2], (cuuint32_t)a.up[1], (cuuint32_t)a.up[0], 1};
         int rc = encode_map_bf16(&map_y, 5, y, dims, st, box, es, "output");
         if (rc != IVX_OK) return rc;
+        map_r = map_y;      // the residual has the output's shape: same map over its own memory
+        if (a.res_tma) {
+            rc = encode_map_bf16(&map_r, 5, const_cast<void *>(residual), dims, st, box, es, "residual");
+            if (rc != IVX_OK) return rc;
+        }
     }
 
     int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -540,7 +650,7 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
                         "cudaFuncSetAttribute");
     if (rc != IVX_OK) return rc;
     const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
-    conv3d_tc_kernel<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(map_x, map_w, map_y, a);
+    conv3d_tc_kernel<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(map_x, map_w, map_y, map_r, a);
     IVX_CHECK_LAUNCH("conv3d_tc launch");
     return IVX_OK;
 }

@@ -206,3 +206,25 @@ def test_graphed_hot_path_replays_the_same_results():
             # partial sums are added with atomics in arrival order
             assert_volume_close(a.float().cpu().numpy(), b.float().cpu().numpy(), rel=BF16_RTOL, atol=1e-3)
     assert len(graphed._graphs) == 1
+
+
+@pytest.mark.parametrize("shape", [(2, 8, 5, 7, 3), (1, 64, 10, 10, 4), (1, 16, 1, 1, 1), (1, 24, 1, 6, 2),
+                                   (3, 4, 4, 3, 5), (1, 12, 3, 4, 2)])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_upsample2x_trilinear_matches_interpolate(shape, dtype):
+    """Both up-sampling kernels (16-byte channel groups per input voxel; the 4-channel per-output one for
+    other channel counts) against F.interpolate(scale_factor=2, 'trilinear') (necks/imvoxelnet.py:359),
+    including one-voxel axes and the clamped borders."""
+    import torch.nn.functional as F
+    from imvoxelnet_b200 import conv
+    torch.manual_seed(13)
+    x = torch.randn(shape, device=DEV)
+    if dtype == torch.bfloat16:
+        x = x.to(dtype).float()
+    want = F.interpolate(x, scale_factor=2, mode='trilinear', align_corners=False)
+    got = conv.from_ndhwc(conv.upsample2x_trilinear(conv.to_ndhwc(x.to(dtype))))
+    assert got.shape == want.shape and got.dtype == dtype
+    if dtype == torch.float32:
+        assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-6)
+    else:   # one rounding to bf16 of the fp32 result
+        assert_volume_close(got.float().cpu().numpy(), want.cpu().numpy(), rel=4e-3)
