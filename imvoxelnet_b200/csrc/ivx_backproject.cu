@@ -204,21 +204,24 @@ __device__ __forceinline__ void zero4(float4 (&acc)[CPL]) {
     for (int i = 0; i < CPL; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 }
 
-template <int G, int CPL>
-__device__ __forceinline__ void gather4(const void *feat, bool bf16, int off, int t, const bool (&ch_ok)[CPL],
-                                        float4 (&r)[CPL]) {
+// One 16-byte unit per lane and step: 4 fp32 channels, or (FB) 8 bf16 channels widened exactly
+// into two float4 -- the sums stay fp32 either way.
+template <int G, int CPL, bool FB>
+__device__ __forceinline__ void gather4(const void *feat, int off, int t, const bool (&ch_ok)[CPL],
+                                        float4 (&r)[CPL * (FB ? 2 : 1)]) {
 #pragma unroll
     for (int i = 0; i < CPL; ++i) {
-        r[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (off >= 0 && ch_ok[i]) {
-            if (!bf16) {
-                r[i] = __ldg(reinterpret_cast<const float4 *>(feat) + off + t + i * G);
-            } else {   // 4 bf16 channels = 8 bytes; widening to fp32 is exact, the sum stays fp32
-                const uint2 u = __ldg(reinterpret_cast<const uint2 *>(feat) + off + t + i * G);
-                const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.x));
-                const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.y));
-                r[i] = make_float4(lo.x, lo.y, hi.x, hi.y);
-            }
+        if constexpr (!FB) {
+            r[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (off >= 0 && ch_ok[i]) r[i] = __ldg(reinterpret_cast<const float4 *>(feat) + off + t + i * G);
+        } else {
+            uint4 u = make_uint4(0u, 0u, 0u, 0u);
+            if (off >= 0 && ch_ok[i]) u = __ldg(reinterpret_cast<const uint4 *>(feat) + off + t + i * G);
+            // bf16 -> fp32 is a 16-bit shift
+            r[2 * i] = make_float4(__uint_as_float(u.x << 16), __uint_as_float(u.x & 0xffff0000u),
+                                   __uint_as_float(u.y << 16), __uint_as_float(u.y & 0xffff0000u));
+            r[2 * i + 1] = make_float4(__uint_as_float(u.z << 16), __uint_as_float(u.z & 0xffff0000u),
+                                       __uint_as_float(u.w << 16), __uint_as_float(u.w & 0xffff0000u));
         }
     }
 }
@@ -235,13 +238,14 @@ __device__ __forceinline__ void add4(float4 (&acc)[CPL], const float4 (&r)[CPL])
 }
 
 // sum / count (count converted to float, :72; 0 where unseen, :74), then store
-template <int G, int CPL, bool DIVIDE, typename OutT>
+template <int G, int CPL, bool DIVIDE, typename OutT, bool FB>
 __device__ __forceinline__ void finish_voxel(const BpArgs &a, OutT *vol, int n, int t, int cnt,
-                                             float4 (&acc)[CPL], const bool (&ch_ok)[CPL]) {
+                                             float4 (&acc)[CPL * (FB ? 2 : 1)], const bool (&ch_ok)[CPL]) {
+    constexpr int NF = FB ? 2 : 1;   // float4 per 16-byte feature unit
     if (DIVIDE && a.reduce == IVX_REDUCE_MEAN && cnt > 1) {
         const float c = (float)cnt;
 #pragma unroll
-        for (int i = 0; i < CPL; ++i) {
+        for (int i = 0; i < CPL * NF; ++i) {
             acc[i].x = __fdiv_rn(acc[i].x, c);
             acc[i].y = __fdiv_rn(acc[i].y, c);
             acc[i].z = __fdiv_rn(acc[i].z, c);
@@ -251,16 +255,31 @@ __device__ __forceinline__ void finish_voxel(const BpArgs &a, OutT *vol, int n, 
     OutT *dst = vol + (long long)n * a.os_n;
 #pragma unroll
     for (int i = 0; i < CPL; ++i)
-        if (ch_ok[i]) store4<OutT>(dst + (t + i * G) * 4, acc[i]);
+        if (ch_ok[i]) {
+            if constexpr (FB && sizeof(OutT) == 2) {   // 8 bf16 channels: one 16-byte streaming store
+                const float4 lo = acc[2 * i], hi = acc[2 * i + 1];
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(lo.x, lo.y), p1 = __floats2bfloat162_rn(lo.z, lo.w);
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(hi.x, hi.y), p3 = __floats2bfloat162_rn(hi.z, hi.w);
+                uint4 u;
+                u.x = *reinterpret_cast<unsigned *>(&p0), u.y = *reinterpret_cast<unsigned *>(&p1);
+                u.z = *reinterpret_cast<unsigned *>(&p2), u.w = *reinterpret_cast<unsigned *>(&p3);
+                __stcs(reinterpret_cast<uint4 *>(dst + (t + i * G) * 8), u);
+            } else {
+#pragma unroll
+                for (int k = 0; k < NF; ++k) store4<OutT>(dst + ((t + i * G) * NF + k) * 4, acc[i * NF + k]);
+            }
+        }
 }
 
-template <int G, int CPL, int MODE, typename OutT>
-__global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const __grid_constant__ BpArgs a) {
+template <int G, int CPL, int MODE, typename OutT, bool FB>
+__global__ void __launch_bounds__(256, (CPL * (FB ? 2 : 1) <= 2 ? 4 : 2)) bp_vec_kernel(const __grid_constant__ BpArgs a) {
+    constexpr int NF = FB ? 2 : 1;             // float4 accumulators per 16-byte feature unit
+    constexpr int ACC = CPL * NF;
     extern __shared__ int smem[];
     constexpr unsigned FULL = 0xffffffffu;
     constexpr int VPI = 32 / G;                // voxels a warp works on at once
-    constexpr int DEPTH = (CPL >= 4) ? 2 : 4;  // MODE_DEEP: pixels in flight per voxel
-    constexpr int WIDTH = (CPL >= 4) ? 1 : (CPL == 2 ? 2 : 4);  // voxels in flight per group
+    constexpr int DEPTH = (ACC >= 4) ? 2 : 4;  // MODE_DEEP: pixels in flight per voxel
+    constexpr int WIDTH = (ACC >= 4) ? 1 : (ACC == 2 ? 2 : 4);  // voxels in flight per group
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -273,8 +292,7 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
     __syncthreads();
     int *table = smem + ((a.V * 12 + 3) & ~3) + warp * T * a.table_stride;
 
-    const bool fb = a.feat_bf16 != 0;
-    const void *feat4 = fb ? static_cast<const void *>(reinterpret_cast<const __nv_bfloat16 *>(a.feat) + b * a.fs_b)
+    const void *feat4 = FB ? static_cast<const void *>(reinterpret_cast<const __nv_bfloat16 *>(a.feat) + b * a.fs_b)
                            : static_cast<const void *>(a.feat + b * a.fs_b);
     OutT *vol = reinterpret_cast<OutT *>(a.vol) + b * a.os_b;
     const int g = lane / G;
@@ -283,7 +301,7 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
 
     bool ch_ok[CPL];
 #pragma unroll
-    for (int i = 0; i < CPL; ++i) ch_ok[i] = (t + i * G) * 4 < a.C;
+    for (int i = 0; i < CPL; ++i) ch_ok[i] = (t + i * G) * 4 * NF < a.C;
 
     for (int tile = blockIdx.x * nwarps + warp; tile < ntiles; tile += gridDim.x * nwarps) {
         const int n0 = tile << a.tile_log2;
@@ -304,7 +322,7 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
             }
             for (int j0 = 0; j0 < T; j0 += VPI * WIDTH) {
                 int o[WIDTH];
-                float4 r[WIDTH][CPL];
+                float4 r[WIDTH][ACC];
 #pragma unroll
                 for (int u = 0; u < WIDTH; ++u) {
                     const int j = j0 + u * VPI + g;
@@ -312,20 +330,20 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
                     if (j >= T) o[u] = -1;
                 }
 #pragma unroll
-                for (int u = 0; u < WIDTH; ++u) gather4<G, CPL>(feat4, fb, o[u], t, ch_ok, r[u]);
+                for (int u = 0; u < WIDTH; ++u) gather4<G, CPL, FB>(feat4, o[u], t, ch_ok, r[u]);
 #pragma unroll
                 for (int u = 0; u < WIDTH; ++u) {
                     const int j = j0 + u * VPI + g;
                     const int n = n0 + j;
                     if (j < T && n < a.N)
-                        finish_voxel<G, CPL, false, OutT>(a, vol, n, t, o[u] >= 0, r[u], ch_ok);
+                        finish_voxel<G, CPL, false, OutT, FB>(a, vol, n, t, o[u] >= 0, r[u], ch_ok);
                 }
             }
         } else if constexpr (MODE == MODE_WIDE) {
             const int my_cnt = fill_table<true>(a, sP, table, b, n0, lane);
             for (int j0 = 0; j0 < T; j0 += VPI * WIDTH) {
                 int cnt[WIDTH];
-                float4 acc[WIDTH][CPL];
+                float4 acc[WIDTH][ACC];
                 int most = 0;
 #pragma unroll
                 for (int u = 0; u < WIDTH; ++u) {
@@ -333,25 +351,25 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
                     cnt[u] = __shfl_sync(FULL, my_cnt, j & 31);
                     if (j >= T || n0 + j >= a.N) cnt[u] = 0;
                     most = max(most, cnt[u]);
-                    zero4<CPL>(acc[u]);
+                    zero4<ACC>(acc[u]);
                 }
                 const int *rows = table + (j0 + g) * a.table_stride;
                 for (int k = 0; k < most; ++k) {
-                    float4 r[WIDTH][CPL];
+                    float4 r[WIDTH][ACC];
 #pragma unroll
                     for (int u = 0; u < WIDTH; ++u) {
                         const int o = (k < cnt[u]) ? rows[u * VPI * a.table_stride + k] : -1;
-                        gather4<G, CPL>(feat4, fb, o, t, ch_ok, r[u]);
+                        gather4<G, CPL, FB>(feat4, o, t, ch_ok, r[u]);
                     }
 #pragma unroll
-                    for (int u = 0; u < WIDTH; ++u) add4<CPL>(acc[u], r[u]);
+                    for (int u = 0; u < WIDTH; ++u) add4<ACC>(acc[u], r[u]);
                 }
 #pragma unroll
                 for (int u = 0; u < WIDTH; ++u) {
                     const int j = j0 + u * VPI + g;
                     const int n = n0 + j;
                     if (j < T && n < a.N)
-                        finish_voxel<G, CPL, true, OutT>(a, vol, n, t, cnt[u], acc[u], ch_ok);
+                        finish_voxel<G, CPL, true, OutT, FB>(a, vol, n, t, cnt[u], acc[u], ch_ok);
                 }
             }
             __syncwarp();  // the table is rewritten by the next tile
@@ -364,19 +382,19 @@ __global__ void __launch_bounds__(256, (CPL <= 2 ? 4 : 2)) bp_vec_kernel(const _
                 int cnt = __shfl_sync(FULL, my_cnt, j & 31);
                 if (!active) cnt = 0;
                 const int *row = table + j * a.table_stride;
-                float4 acc[CPL];
-                zero4<CPL>(acc);
+                float4 acc[ACC];
+                zero4<ACC>(acc);
                 for (int k0 = 0; k0 < cnt; k0 += DEPTH) {
-                    float4 r[DEPTH][CPL];
+                    float4 r[DEPTH][ACC];
 #pragma unroll
                     for (int u = 0; u < DEPTH; ++u) {
                         const int o = (k0 + u < cnt) ? row[k0 + u] : -1;
-                        gather4<G, CPL>(feat4, fb, o, t, ch_ok, r[u]);
+                        gather4<G, CPL, FB>(feat4, o, t, ch_ok, r[u]);
                     }
 #pragma unroll
-                    for (int u = 0; u < DEPTH; ++u) add4<CPL>(acc, r[u]);  // ascending view order
+                    for (int u = 0; u < DEPTH; ++u) add4<ACC>(acc, r[u]);  // ascending view order
                 }
-                if (active) finish_voxel<G, CPL, true, OutT>(a, vol, n, t, cnt, acc, ch_ok);
+                if (active) finish_voxel<G, CPL, true, OutT, FB>(a, vol, n, t, cnt, acc, ch_ok);
             }
             __syncwarp();  // the table is rewritten by the next tile
         }
@@ -620,46 +638,48 @@ static int pick_tile_log2(long long n_points, int n_scenes, int table_stride) {
     return lg;
 }
 
-template <int MODE, typename OutT>
+template <int MODE, typename OutT, bool FB>
 static void *pick_vec_kernel(int C) {
-    const int c4 = (C + 3) / 4;
-    if (c4 <= 8) return (void *)bp_vec_kernel<8, 1, MODE, OutT>;
-    if (c4 <= 16) return (void *)bp_vec_kernel<16, 1, MODE, OutT>;
-    if (c4 <= 32) return (void *)bp_vec_kernel<32, 1, MODE, OutT>;
-    if (c4 <= 64) return (void *)bp_vec_kernel<32, 2, MODE, OutT>;
-    if (c4 <= 128) return (void *)bp_vec_kernel<32, 4, MODE, OutT>;
-    if (c4 <= 256) return (void *)bp_vec_kernel<32, 8, MODE, OutT>;
+    const int units = FB ? (C + 7) / 8 : (C + 3) / 4;   // 16-byte units per pixel
+    if (units <= 8) return (void *)bp_vec_kernel<8, 1, MODE, OutT, FB>;
+    if (units <= 16) return (void *)bp_vec_kernel<16, 1, MODE, OutT, FB>;
+    if (units <= 32) return (void *)bp_vec_kernel<32, 1, MODE, OutT, FB>;
+    if (units <= 64) return (void *)bp_vec_kernel<32, 2, MODE, OutT, FB>;
+    if (units <= 128) return (void *)bp_vec_kernel<32, 4, MODE, OutT, FB>;
+    if (!FB && units <= 256) return (void *)bp_vec_kernel<32, 8, MODE, OutT, false>;
     return nullptr;
 }
 
 constexpr int kWideMaxViews = 8;  // up to here most voxels are hit by 0..2 views
 
-template <typename OutT>
+template <typename OutT, bool FB>
 static void *pick_vec_kernel(int C, int V) {
-    if (V == 1) return pick_vec_kernel<MODE_SINGLE, OutT>(C);
-    if (V <= kWideMaxViews) return pick_vec_kernel<MODE_WIDE, OutT>(C);
-    return pick_vec_kernel<MODE_DEEP, OutT>(C);
+    if (V == 1) return pick_vec_kernel<MODE_SINGLE, OutT, FB>(C);
+    if (V <= kWideMaxViews) return pick_vec_kernel<MODE_WIDE, OutT, FB>(C);
+    return pick_vec_kernel<MODE_DEEP, OutT, FB>(C);
 }
 
 static bool aligned16(const void *p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 
 // One launch over at most IVX_MAX_SCENES_PER_LAUNCH scenes.
 static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t stream, bool backward = false) {
-    const bool feat_vec = a.fs_c == 1 && a.C % 4 == 0 &&
-                          (a.feat_bf16 ? reinterpret_cast<uintptr_t>(a.feat) % 8 == 0 : aligned16(a.feat)) &&
-                          a.fs_b % 4 == 0 &&
-                          a.fs_v % 4 == 0 && a.fs_h % 4 == 0 && a.fs_w % 4 == 0;
+    const int upe = a.feat_bf16 ? 8 : 4;   // elements per 16-byte unit of the feature maps
+    const bool feat_vec = a.fs_c == 1 && a.C % upe == 0 && aligned16(a.feat) && a.fs_b % upe == 0 &&
+                          a.fs_v % upe == 0 && a.fs_h % upe == 0 && a.fs_w % upe == 0;
     const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
-    const bool vol_vec = a.os_c == 1 && a.os_b % 4 == 0 && a.os_n % 4 == 0 &&
-                         (reinterpret_cast<uintptr_t>(a.vol) % (4 * esz)) == 0;
+    const int vupe = (a.feat_bf16 && vol_dtype == IVX_BF16) ? 8 : 4;   // elements per vector store
+    const bool vol_vec = a.os_c == 1 && a.os_b % vupe == 0 && a.os_n % vupe == 0 &&
+                         (reinterpret_cast<uintptr_t>(a.vol) % (vupe * esz)) == 0;
     void *kernel = nullptr;
     if (backward) {
         if (!(feat_vec && vol_vec) || vol_dtype != IVX_F32 || (kernel = pick_backward_kernel(a.C)) == nullptr)
             return fail(IVX_ERR_UNSUPPORTED,
                         "backward needs channels-last fp32 gradients with C %% 4 == 0 and C <= 1024");
     } else if (feat_vec && vol_vec)
-        kernel = vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16>(a.C, a.V)
-                                        : pick_vec_kernel<float>(a.C, a.V);
+        kernel = a.feat_bf16 ? (vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16, true>(a.C, a.V)
+                                                      : pick_vec_kernel<float, true>(a.C, a.V))
+                             : (vol_dtype == IVX_BF16 ? pick_vec_kernel<__nv_bfloat16, false>(a.C, a.V)
+                                                      : pick_vec_kernel<float, false>(a.C, a.V));
     if (kernel != nullptr) {
         // table entries are int32 offsets in float4 units inside one scene's block
         long long hmax = 0, wmax = 0;
@@ -667,12 +687,14 @@ static int launch_scenes(BpArgs &a, int n_scenes, int vol_dtype, cudaStream_t st
             hmax = a.hw[b][0] > hmax ? a.hw[b][0] : hmax;
             wmax = a.hw[b][1] > wmax ? a.hw[b][1] : wmax;
         }
-        if ((llabs(a.fs_v) * a.V + llabs(a.fs_h) * hmax + llabs(a.fs_w) * wmax) / 4 >= (1ll << 31))
+        if ((llabs(a.fs_v) * a.V + llabs(a.fs_h) * hmax + llabs(a.fs_w) * wmax) / upe >= (1ll << 31))
             return fail(IVX_ERR_UNSUPPORTED, "feature block of one scene exceeds 2^33 elements");
-        a.q_v = (int)(a.fs_v / 4), a.q_h = (int)(a.fs_h / 4), a.q_w = (int)(a.fs_w / 4);
+        const int q = backward ? 4 : upe;
+        a.q_v = (int)(a.fs_v / q), a.q_h = (int)(a.fs_h / q), a.q_w = (int)(a.fs_w / q);
     }
     if (kernel == nullptr && a.feat_bf16)
-        return fail(IVX_ERR_UNSUPPORTED, "bf16 feature maps need the channels-last layout (C %% 4 == 0, C <= 1024)");
+        return fail(IVX_ERR_UNSUPPORTED,
+                    "bf16 feature maps need the channels-last layout, C %% 8 == 0, C <= 1024 and 16-byte aligned rows");
     if (kernel == nullptr) {
         if (vol_dtype != IVX_F32)
             return fail(IVX_ERR_UNSUPPORTED,

@@ -504,17 +504,26 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     a.batch = p->batch;
     pick_box(row_dims, p->transposed ? p->stride : ld_stride, a.box, a.tiles);
     const long long out_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
-    // split-K: a layer with fewer tiles than ~2/3 of the SMs spreads each tile's k-steps over
-    // several CTAs (needs a workspace; the caller may not have one -> k_splits reset to 1 later)
+    // split-K: the persistent grid runs ceil(work items / 148) waves, so a layer whose tile count is
+    // small or just above a multiple of the SM count leaves SMs idle in the last wave (200 tiles =
+    // 1.35 waves cost 2).  Sharing each tile's k-steps between k_splits CTAs changes the item count;
+    // pick the split that minimises waves x k-steps per item, charging 3% per extra split for the
+    // fp32 partials that go through the L2 workspace (needs a workspace; the caller may not have
+    // one -> k_splits reset to 1 later).
     const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
     a.k_splits = 1;
     a.steps_per_split = k_steps;
-    if (out_tiles * 3 <= kNumSMs * 2 && k_steps >= 8) {
-        int want = (int)(kNumSMs / out_tiles);
-        if (want > k_steps / 4) want = k_steps / 4;            // at least 4 k-steps per CTA
-        if (want > 1) {
-            a.steps_per_split = (k_steps + want - 1) / want;
-            a.k_splits = (k_steps + a.steps_per_split - 1) / a.steps_per_split;
+    {
+        auto cost = [&](int splits, int steps) {
+            const long long waves = (out_tiles * splits + kNumSMs - 1) / kNumSMs;
+            return (double)waves * (steps + 2.0) * (1.0 + 0.03 * (splits - 1));   // + 2: per-item epilogue
+        };
+        double best = cost(1, k_steps);
+        for (int want = 2; want <= 8 && want * 4 <= k_steps; ++want) {           // at least 4 k-steps per CTA
+            const int steps = (k_steps + want - 1) / want;
+            const int splits = (k_steps + steps - 1) / steps;
+            const double c = cost(splits, steps);
+            if (c < 0.93 * best) best = c, a.k_splits = splits, a.steps_per_split = steps;
         }
     }
     a.n_tiles = out_tiles * a.k_splits;

@@ -199,8 +199,8 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
     if features.dtype not in (torch.float32, torch.bfloat16) or features.dim() != 5:
         raise TypeError("features must be a float32 (or channels-last bfloat16) [B,V,C,Hf,Wf] tensor")
     bf16_maps = features.dtype == torch.bfloat16
-    if bf16_maps and (features.stride(2) != 1 or features.shape[2] % 4):
-        raise TypeError("bfloat16 features must be channels-last with C % 4 == 0")
+    if bf16_maps and (features.stride(2) != 1 or features.shape[2] % 8):
+        raise TypeError("bfloat16 features must be channels-last with C % 8 == 0")
     b, v, c = features.shape[:3]
     dev = features.device
     xs, ys, zs = (int(t) for t in n_voxels)

@@ -132,7 +132,7 @@ IVX_API int ivx_backproject_scenes(const float *feat, const int64_t *feat_stride
 
 /*
  * ivx_backproject_scenes_bf16 -- ivx_backproject_scenes on bf16 feature maps
- * (channels-last, C % 4 == 0): what a bf16 2D backbone emits.  The reference
+ * (channels-last, C % 8 == 0, 16-byte aligned pixels): what a bf16 2D backbone emits.  The reference
  * keeps fp32 maps (its FPN output, detectors/imvoxelnet.py:50-51); with bf16
  * maps the gather moves half the bytes.  Values are widened exactly and summed
  * in fp32, so the result equals ivx_backproject_scenes on the widened maps.

@@ -156,4 +156,5 @@ def test_split_k_tail_layers_and_workspace_reuse(cin, cout, dims, stride, batch)
     assert any(w is not False for w in fused._ws.values()), "this shape was expected to use split-K"
     for got in outs:
         assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-2, atol=1e-3)
-    assert torch.equal(outs[0], outs[2]) or (outs[0] - outs[2]).abs().max() < 1e-2
+    # the order of the fp32 atomics is not fixed: two calls may differ by one bf16 rounding (2^-8 relative)
+    assert torch.equal(outs[0], outs[2]) or (outs[0] - outs[2]).abs().max() <= 2.0 ** -7 * outs[0].abs().max()
