@@ -74,6 +74,9 @@ class ImVoxelNet(_Base):
             self.bbox_head = build_head(bbox_head)
         if self.bbox_head is not None:
             self.bbox_head.voxel_size = voxel_size
+            from . import heads
+            if heads.supports(self.bbox_head):      # ImVoxelHead / ImVoxelHeadV2: fused convolution tail
+                heads.accelerate(self.bbox_head)
         self.head_2d = (head_2d if isinstance(head_2d, nn.Module) else build_head(head_2d)) \
             if head_2d is not None else None
         self.n_voxels = n_voxels

@@ -19,13 +19,16 @@ parameter holders with exactly those names (same state-dict keys as the
 reference heads' convolution part) for use without mmdet.  Losses, target
 assignment, box decoding and NMS stay the reference's PyTorch code.
 """
+import types
+
 import torch
 from torch import nn
 
 from . import _lib
 from .conv import FusedConv, to_ndhwc, _DT, _stream
 
-__all__ = ["head_forward", "resize_valid", "head_scores", "HeadConvsV2", "HeadConvsV1", "launch_count"]
+__all__ = ["head_forward", "resize_valid", "head_scores", "supports", "accelerate", "HeadConvsV2", "HeadConvsV1",
+           "launch_count"]
 
 _launches = 0
 N_DISTANCES = 6     # reg_final[:, :6] are the exp()-ed face distances, the rest (angle) stays raw
@@ -157,6 +160,26 @@ def head_forward(head, xs):
     with torch.cuda.device(xs[0].device):
         outs = [_forward_single(head, plan, x, s) for x, s in zip(xs, head.scales)]
     return tuple(map(list, zip(*outs)))
+
+
+def supports(head):
+    """Does ``head`` look like one of the reference's ImVoxelHead / ImVoxelHeadV2 classes?"""
+    convs = [getattr(head, n, None) for n in ("centerness_conv", "reg_conv", "cls_conv")]
+    if not all(isinstance(c, nn.Conv3d) for c in convs) or not hasattr(head, "scales"):
+        return False
+    if not all(tuple(c.kernel_size) == (3, 3, 3) and tuple(c.padding) == (1, 1, 1) and tuple(c.stride) == (1, 1, 1)
+               for c in convs):
+        return False
+    return hasattr(head, "reg_convs") == hasattr(head, "cls_convs")
+
+
+def accelerate(head):
+    """Route ``head(xs)`` (and with it ``forward_train`` / ``get_bboxes`` callers) through ``head_forward``.
+    Parameters, state-dict keys and every other method of the head stay as they are."""
+    if not supports(head):
+        raise TypeError(f"{type(head).__name__} does not have the ImVoxelHead convolution layout")
+    object.__setattr__(head, "forward", types.MethodType(head_forward, head))   # survives copy.deepcopy
+    return head
 
 
 def resize_valid(valid, size):

@@ -191,3 +191,25 @@ def test_head_training_gradients_match_autograd(version):
         assert q.grad is not None, k
         assert_volume_close(q.grad.cpu().numpy(), p.grad.cpu().numpy(), rel=1e-4)
 
+
+
+def test_accelerate_routes_forward_and_survives_deepcopy():
+    ref = torch_heads.randomise(torch_heads.HeadV2(4, 8, 6, 2), 12).eval().to(DEV)
+    plain = copy.deepcopy(ref)
+    assert heads.supports(ref) and not heads.supports(torch.nn.Conv3d(1, 1, 3))
+    heads.accelerate(ref)
+    xs = [torch.randn(1, 8, 6, 6, 4, device=DEV), torch.randn(1, 8, 3, 3, 2, device=DEV)]
+    before = heads.launch_count()
+    with torch.no_grad():
+        got, want = ref(xs), plain(xs)
+    assert heads.launch_count() - before == 6          # the module call went through the fused tail
+    clone = copy.deepcopy(ref)
+    assert clone.forward.__self__ is clone             # the copy runs on its own parameters
+    with torch.no_grad():
+        clone.cls_conv.bias.add_(2.0)
+        moved = clone(xs)
+    for u, v in zip(got, want):
+        for p, q in zip(u, v):
+            assert_volume_close(p.cpu().numpy(), q.cpu().numpy(), rel=2e-5)
+    assert_volume_close((moved[2][0] - got[2][0]).cpu().numpy(), np.full(got[2][0].shape, 2.0, np.float32), rel=1e-5)
+    assert list(ref.state_dict().keys()) == list(plain.state_dict().keys())
