@@ -67,6 +67,7 @@ PROTOTYPES["ivx_finalize_mean_peers"] = [c_void_p, c_void_p, c_int, c_void_p, c_
 PROTOTYPES["ivx_conv3d_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p]
 PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"] = PROTOTYPES["ivx_conv3d_ndhwc"][:7] + [c_void_p, c_int64, c_void_p]
+PROTOTYPES["ivx_conv3d_ndhwc_tf32_tc"] = PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"]
 PROTOTYPES["ivx_conv3d_tc_workspace_bytes"] = [_ConvP]
 c_float = ctypes.c_float
 PROTOTYPES["ivx_channel_moments_ndhwc"] = [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p]

@@ -12,12 +12,28 @@ from torch import nn
 
 from . import _lib
 
-__all__ = ["FusedConv", "upsample2x_trilinear", "to_ndhwc", "from_ndhwc", "launch_count"]
+import contextlib
+
+__all__ = ["FusedConv", "upsample2x_trilinear", "to_ndhwc", "from_ndhwc", "launch_count", "tf32"]
 
 _launches = 0
 #: bf16 layers with c_in, c_out multiples of 64 run on tcgen05; False forces the CUDA-core kernel
 USE_TENSOR_CORES = True
 _DT = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}
+_TF32 = False
+
+
+@contextlib.contextmanager
+def tf32(enabled=True):
+    """Inside: fp32 layers with c_in % 32 == 0 and c_out % 64 == 0 run on the tensor cores with tf32
+    math (``ivx_conv3d_ndhwc_tf32_tc``, about 1e-3 of the fp32 result), like
+    ``torch.backends.cudnn.allow_tf32``.  The necks' ``precision = "tf32"`` switches it on."""
+    global _TF32
+    old, _TF32 = _TF32, bool(enabled)
+    try:
+        yield
+    finally:
+        _TF32 = old
 
 
 def launch_count():
@@ -54,6 +70,7 @@ class FusedConv:
             assert tuple(conv.dilation) == (1, 1, 1) and conv.groups == 1
         self._packed = None
         self._packed_tc = None
+        self._packed_tf32 = None
         self._ws = {}
 
     # ---- parameter packing (cached until a parameter or buffer changes) ----
@@ -85,7 +102,7 @@ class FusedConv:
                 elif bias is not None:
                     shift = bias.detach().to(device, torch.float32).contiguous()
             self._packed = (key, wp, scale, shift)
-            self._packed_tc = None
+            self._packed_tc = self._packed_tf32 = None
         return self._packed[1:]
 
     def packed_tc(self, device):
@@ -100,10 +117,21 @@ class FusedConv:
                     self._packed_tc = w.permute(0, 2, 3, 4, 1).contiguous().to(torch.bfloat16)
         return self._packed_tc, scale, shift
 
+    def packed_tf32(self, device):
+        """fp32 weights in the tensor-core layout (+ fp32 scale/shift) for the tf32 kernel."""
+        _, scale, shift = self.packed(device)
+        if self._packed_tf32 is None:
+            with torch.no_grad():
+                w = self.conv.weight.detach().to(device=device, dtype=torch.float32)
+                # [taps][Cout][Cin] for transposed layers, [Cout][taps][Cin] otherwise
+                perm = (2, 3, 4, 1, 0) if self.transposed else (0, 2, 3, 4, 1)
+                self._packed_tf32 = w.permute(*perm).contiguous()
+        return self._packed_tf32, scale, shift
+
     def _workspace(self, params, device):
         """Split-K scratch of this layer for this geometry: zero-filled once, the kernel
         leaves it zero-filled (include/ivx.h); None when the layer does not split."""
-        key = (str(device), params.batch, tuple(params.in_dims))
+        key = (str(device), bytes(params))      # every field of the geometry decides the split
         ws = self._ws.get(key)
         if ws is None:
             nbytes = _lib.lib().ivx_conv3d_tc_workspace_bytes(params)
@@ -117,6 +145,12 @@ class FusedConv:
         return (x.dtype == torch.bfloat16 and out_dtype == torch.bfloat16
                 and self.conv.in_channels % 64 == 0 and self.conv.out_channels % 64 == 0
                 and USE_TENSOR_CORES)
+
+    def tf32_eligible(self, x, out_dtype, residual=None):
+        if self.transposed and residual is not None:
+            return False
+        return (_TF32 and x.dtype == torch.float32 and out_dtype == torch.float32
+                and self.conv.in_channels % 32 == 0 and self.conv.out_channels % 64 == 0)
 
     def out_dims(self, in_dims):
         k, s = _triple(self.conv.kernel_size), _triple(self.conv.stride)
@@ -172,6 +206,14 @@ class FusedConv:
                     shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(),
                     ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
                     _stream()), "ivx_conv3d_ndhwc_bf16_tc")
+            elif self.tf32_eligible(x, out_dtype, residual):
+                wt, scale, shift = self.packed_tf32(x.device)
+                ws = self._workspace(p, x.device)
+                _lib.check(_lib.lib().ivx_conv3d_ndhwc_tf32_tc(
+                    p, x.data_ptr(), wt.data_ptr(), scale.data_ptr() if scale is not None else None,
+                    shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(),
+                    ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
+                    _stream()), "ivx_conv3d_ndhwc_tf32_tc")
             else:
                 _lib.check(_lib.lib().ivx_conv3d_ndhwc(
                     p, x.data_ptr(), wp.data_ptr(), scale.data_ptr() if scale is not None else None,

@@ -52,8 +52,9 @@ struct TcArgs {
     int relu, residual_after_act;
     float post_scale;
     const float *scale, *shift;
-    const __nv_bfloat16 *res;
-    int n_slabs;                // output staging slabs: 2, or 3..8 when the residual comes in by TMA
+    const void *res;            // residual, in the layer's storage type
+    int n_slabs;                // output staging slots (64 channels each): 2 (1 if short of shared memory),
+                                // or 3..8 when the residual comes in by TMA
     int res_tma;                // residual tiles are TMA-loaded into the slabs (needs n_slabs >= 3)
     // transposed layers (ConvTranspose3d, kernel == stride): rows are INPUT voxels, the GEMM
     // columns are (tap, c_out); every n-tile lies inside one tap and is stored with that
@@ -125,6 +126,32 @@ __device__ __forceinline__ uint4 epilogue8(const uint32_t *v, uint32_t ss_addr, 
     return o;
 }
 
+// The same for fp32 storage (tf32 layers): four channels per 16-byte cell.
+template <int RES, bool POST>
+__device__ __forceinline__ uint4 epilogue4(const uint32_t *v, uint32_t ss_addr, uint4 res, float act_floor,
+                                           float post_scale) {
+    float f[4];
+#pragma unroll
+    for (int e = 0; e < 4; e += 2) {
+        const uint4 ss = lds128(ss_addr + (uint32_t)e * 8);
+        f[e] = fmaf(__uint_as_float(v[e]), __uint_as_float(ss.x), __uint_as_float(ss.y));
+        f[e + 1] = fmaf(__uint_as_float(v[e + 1]), __uint_as_float(ss.z), __uint_as_float(ss.w));
+    }
+    const float r[4] = {__uint_as_float(res.x), __uint_as_float(res.y), __uint_as_float(res.z), __uint_as_float(res.w)};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+        if (RES == 1) f[e] += r[e];
+        f[e] = fmaxf(f[e], act_floor);
+        if (RES == 2) f[e] += r[e];
+        if (POST) f[e] *= post_scale;
+    }
+    return make_uint4(__float_as_uint(f[0]), __float_as_uint(f[1]), __float_as_uint(f[2]), __float_as_uint(f[3]));
+}
+
+// TF32 = false: bf16 storage, kind::f16 MMAs, 64 channels per 128-byte k-step and per output slab.
+// TF32 = true : fp32 storage, kind::tf32 MMAs (the TMA rounds the operands to tf32), 32 channels per
+//               k-step; a 64-channel output chunk is two 32-channel slabs, one per epilogue warp half.
+template <bool TF32>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_r,
@@ -135,8 +162,10 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const int b_bytes = a.n_tile * 128;
     const int stage_bytes = TC_A_BYTES + b_bytes;
     uint8_t *stage_base = smem;
-    uint8_t *slab_base = smem + (size_t)a.stages * stage_bytes;  // n_slabs output slabs of 128 x 128 B
-    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + (size_t)a.n_slabs * TC_A_BYTES);
+    constexpr int EK = TF32 ? 32 : 64;    // channels per k-step (one 128-byte swizzle row)
+    constexpr int SPC = TF32 ? 2 : 1;     // 128-byte-wide slabs per 64-channel output chunk
+    uint8_t *slab_base = smem + (size_t)a.stages * stage_bytes;  // n_slabs slots of SPC slabs of 128 x 128 B
+    uint64_t *bars = reinterpret_cast<uint64_t *>(slab_base + (size_t)a.n_slabs * SPC * TC_A_BYTES);
     uint64_t *full_bar = bars, *empty_bar = bars + a.stages;
     uint64_t *acc_full = bars + 2 * a.stages, *acc_empty = acc_full + 2;
     uint64_t *res_bar = acc_empty + 2;               // residual tile landed in slab s (up to 8 slabs)
@@ -170,7 +199,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     const uint32_t tmem_base = *tmem_slot;
     const int acc_stride = tmem_cols / 2;  // columns between the two accumulators
 
-    const int k_chunks = a.c_in / TC_KCHUNK;
+    const int k_chunks = a.c_in / EK;
     const int n_taps = a.taps[0] * a.taps[1] * a.taps[2];
     const int k_steps = n_taps * k_chunks;
 
@@ -193,8 +222,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     const uint32_t bar = smem_u32(full_bar + stage);
                     const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
                     mbar_expect_tx(bar, (uint32_t)(a.box[0] * a.box[1] * a.box[2] * 128 + b_bytes));
-                    tma_load_5d(sa, &map_x, bar, kc * TC_KCHUNK, cz, cy, cx, tc.b);
-                    tma_load_2d(sa + TC_A_BYTES, &map_w, bar, tap * a.c_in + kc * TC_KCHUNK, tc.n0);
+                    tma_load_5d(sa, &map_x, bar, kc * EK, cz, cy, cx, tc.b);
+                    tma_load_2d(sa + TC_A_BYTES, &map_w, bar, tap * a.c_in + kc * EK, tc.n0);
                     if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
                 }
             }
@@ -202,7 +231,7 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
     } else if (warp == 1) {
         // ------------------------------ MMA issuer ------------------------------
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc(a.n_tile);
+            const uint32_t idesc = TF32 ? umma_idesc_tf32(a.n_tile) : umma_idesc(a.n_tile);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
                 mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);  // epilogue drained this accumulator
@@ -216,8 +245,10 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
                     const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TC_A_BYTES);
 #pragma unroll
-                    for (int k = 0; k < TC_KCHUNK / 16; ++k)  // +32 bytes per K=16 slice inside the swizzle row
-                        umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+                    for (int k = 0; k < 4; ++k) {   // +32 bytes per MMA (K = 16 bf16 / 8 tf32) inside the swizzle row
+                        if (TF32) umma_tf32(d_tmem, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+                        else umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+                    }
                     umma_commit(smem_u32(empty_bar + stage));  // frees the smem stage when the MMAs retire
                     if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
                 }
@@ -250,9 +281,10 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const TileCoord c2 = decode_tile(a, t2);
             const int into = (int)(ci % a.n_slabs);
             const uint32_t bar = smem_u32(res_bar + into);
-            mbar_expect_tx(bar, (uint32_t)(box_rows * 128));
-            tma_load_5d(smem_u32(slab_base + (size_t)into * TC_A_BYTES), &map_r, bar,
-                        c2.n0 + (int)(ci % chunks_per_tile) * 64, c2.z0, c2.y0, c2.x0, c2.b);
+            mbar_expect_tx(bar, (uint32_t)(box_rows * 128 * SPC));
+            for (int sl = 0; sl < SPC; ++sl)
+                tma_load_5d(smem_u32(slab_base + (size_t)(into * SPC + sl) * TC_A_BYTES), &map_r, bar,
+                            c2.n0 + (int)(ci % chunks_per_tile) * 64 + sl * 32, c2.z0, c2.y0, c2.x0, c2.b);
         };
         if (a.res_tma && epi_leader)
             for (int ci = 0; ci < a.n_slabs - 1; ++ci) request_residual(ci);
@@ -294,7 +326,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 __threadfence();              // phase B (last CTA): all partials are visible
             }
             for (int c0 = 0; c0 < a.n_tile; c0 += 64) {
-                uint8_t *slab_ptr = slab_base + slab * TC_A_BYTES;
+                uint8_t *slot_ptr = slab_base + (size_t)slab * SPC * TC_A_BYTES;
+                uint8_t *slab_ptr = slot_ptr + (TF32 ? half * TC_A_BYTES : 0);   // the slab this warp writes
                 // (scale, shift) of this chunk's 64 channels -> shared memory (everyone is past the
                 // previous chunk's barrier, so nobody still reads the old ones)
                 if (epi_tid < 64) {
@@ -303,7 +336,10 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 }
                 // the TMA store that last read this slab must be done before we overwrite it (with the
                 // residual by TMA that was checked before its load was issued)
-                if (!a.res_tma && epi_leader) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                if (!a.res_tma && epi_leader) {
+                    if (a.n_slabs > 1) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+                    else asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+                }
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (a.res_tma) {   // the residual of this chunk has landed in the slab
                     mbar_wait(smem_u32(res_bar + slab), (res_phase >> slab) & 1u);
@@ -330,17 +366,35 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     auto run = [&](auto res_c, auto post_c) {
                         constexpr int RES = decltype(res_c)::value;
                         constexpr bool POST = decltype(post_c)::value;
+                        if constexpr (!TF32) {
 #pragma unroll
-                        for (int j = 0; j < 32; j += 8) {
-                            const int chunk = (h + j) >> 3;  // 16-byte chunk inside the 128-byte row
-                            const uint32_t cell = row_addr + ((chunk ^ (row & 7)) << 4);
-                            uint4 u = make_uint4(0u, 0u, 0u, 0u);
-                            if (RES != 0) {
-                                if (a.res_tma) u = lds128(cell);
-                                else if (row_ok) u = __ldg(reinterpret_cast<const uint4 *>(a.res + ovox * a.c_out + ch + j));
+                            for (int j = 0; j < 32; j += 8) {
+                                const int chunk = (h + j) >> 3;  // 16-byte chunk inside the 128-byte row
+                                const uint32_t cell = row_addr + ((chunk ^ (row & 7)) << 4);
+                                uint4 u = make_uint4(0u, 0u, 0u, 0u);
+                                if (RES != 0) {
+                                    if (a.res_tma) u = lds128(cell);
+                                    else if (row_ok)
+                                        u = __ldg(reinterpret_cast<const uint4 *>(
+                                            static_cast<const __nv_bfloat16 *>(a.res) + ovox * a.c_out + ch + j));
+                                }
+                                sts128(cell, epilogue8<RES, POST>(v + j, ss_addr + (uint32_t)(h + j) * 8, u, act_floor,
+                                                                  a.post_scale));
                             }
-                            sts128(cell, epilogue8<RES, POST>(v + j, ss_addr + (uint32_t)(h + j) * 8, u, act_floor,
-                                                              a.post_scale));
+                        } else {   // this warp's 32 channels are one whole 128-byte row of its own slab
+#pragma unroll
+                            for (int j = 0; j < 32; j += 4) {
+                                const uint32_t cell = row_addr + (((j >> 2) ^ (row & 7)) << 4);
+                                uint4 u = make_uint4(0u, 0u, 0u, 0u);
+                                if (RES != 0) {
+                                    if (a.res_tma) u = lds128(cell);
+                                    else if (row_ok)
+                                        u = __ldg(reinterpret_cast<const uint4 *>(
+                                            static_cast<const float *>(a.res) + ovox * a.c_out + ch + j));
+                                }
+                                sts128(cell, epilogue4<RES, POST>(v + j, ss_addr + (uint32_t)(h + j) * 8, u, act_floor,
+                                                                  a.post_scale));
+                            }
                         }
                     };
                     using std::integral_constant;
@@ -356,11 +410,14 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // st.shared -> visible to TMA
                 asm volatile("bar.sync 1, 256;" ::: "memory");
                 if (epi_leader) {
-                    if (a.transposed)
-                        tma_store_5d(&map_y, smem_u32(slab_ptr), ch0 + c0, tc.z0 * a.up[2] + tkz,
-                                     tc.y0 * a.up[1] + tky, tc.x0 * a.up[0] + tkx, tc.b);
-                    else
-                        tma_store_5d(&map_y, smem_u32(slab_ptr), tc.n0 + c0, tc.z0, tc.y0, tc.x0, tc.b);
+                    for (int sl = 0; sl < SPC; ++sl) {
+                        const uint32_t src = smem_u32(slot_ptr + (size_t)sl * TC_A_BYTES);
+                        if (a.transposed)
+                            tma_store_5d(&map_y, src, ch0 + c0 + sl * 32, tc.z0 * a.up[2] + tkz,
+                                         tc.y0 * a.up[1] + tky, tc.x0 * a.up[0] + tkx, tc.b);
+                        else
+                            tma_store_5d(&map_y, src, tc.n0 + c0 + sl * 32, tc.z0, tc.y0, tc.x0, tc.b);
+                    }
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                     if (a.res_tma) {   // once the store of the previous chunk has drained, its slab takes a new chunk
                         asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
@@ -404,9 +461,16 @@ static EncodeTiledFn encode_tiled_fn() {
 int encode_map_bf16(CUtensorMap *map, int rank, void *base, const cuuint64_t *dims,
                       const cuuint64_t *strides_bytes, const cuuint32_t *box, const cuuint32_t *estrides,
                       const char *what) {
+    return encode_map_sw128(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, base, dims, strides_bytes, box, estrides,
+                            what);
+}
+
+int encode_map_sw128(CUtensorMap *map, CUtensorMapDataType dtype, int rank, void *base, const cuuint64_t *dims,
+                     const cuuint64_t *strides_bytes, const cuuint32_t *box, const cuuint32_t *estrides,
+                     const char *what) {
     EncodeTiledFn fn = encode_tiled_fn();
     if (fn == nullptr) return fail(IVX_ERR_CUDA, "cuTensorMapEncodeTiled is not available from the driver");
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, base, dims, strides_bytes, box,
+    CUresult r = fn(map, dtype, (cuuint32_t)rank, base, dims, strides_bytes, box,
                     estrides, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(IVX_ERR_CUDA, "cuTensorMapEncodeTiled(%s) failed with %d", what, (int)r);
@@ -447,10 +511,13 @@ using namespace ivx;
 
 static int validate_tc(const ivx_conv3d_params *p, bool has_residual) {
     IVX_REQUIRE(p != nullptr, "NULL params");
-    if (p->in_dtype != IVX_BF16 || p->out_dtype != IVX_BF16)
-        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in and out only");
-    if (p->c_in % TC_KCHUNK != 0 || p->c_out % 64 != 0)
-        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: c_in and c_out must be multiples of 64");
+    const bool bf16 = p->in_dtype == IVX_BF16 && p->out_dtype == IVX_BF16;
+    const bool tf32 = p->in_dtype == IVX_F32 && p->out_dtype == IVX_F32;
+    if (!bf16 && !tf32)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in and out, or fp32 in and out (tf32 math)");
+    if (p->c_in % (bf16 ? 64 : 32) != 0 || p->c_out % 64 != 0)
+        return fail(IVX_ERR_UNSUPPORTED,
+                    "tensor-core path: c_in must be a multiple of 64 (bf16) or 32 (tf32), c_out of 64");
     if (p->transposed && has_residual)
         return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: transposed layers take no residual");
     for (int d = 0; d < 3; ++d) {
@@ -469,6 +536,7 @@ static int validate_tc(const ivx_conv3d_params *p, bool has_residual) {
 
 // does the halo-reuse kernel take this layer?  (IVX_TC_HALO=0 keeps everything on the per-tap one)
 static bool use_halo(const ivx_conv3d_params *p, int perm[3], int *mt) {
+    if (p->in_dtype != IVX_BF16) return false;   // the halo kernel is bf16 only
     static const bool halo_on = [] {
         const char *e = getenv("IVX_TC_HALO");
         return e == nullptr || e[0] != '0';
@@ -510,7 +578,7 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     // pick the split that minimises waves x k-steps per item, charging 3% per extra split for the
     // fp32 partials that go through the L2 workspace (needs a workspace; the caller may not have
     // one -> k_splits reset to 1 later).
-    const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
+    const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / (p->in_dtype == IVX_BF16 ? 64 : 32));
     a.k_splits = 1;
     a.steps_per_split = k_steps;
     {
@@ -542,25 +610,21 @@ extern "C" int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *p) {
     return out_tiles * TC_ROWS * a.n_tile * (int64_t)sizeof(float) + out_tiles * (int64_t)sizeof(unsigned);
 }
 
-extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *x, const void *weight_bf16,
-                                        const float *scale, const float *shift, const void *residual,
-                                        void *y, void *workspace, int64_t workspace_bytes, void *stream) {
-    IVX_REQUIRE(p && x && weight_bf16 && y, "NULL argument");
-    int rc0 = validate_tc(p, residual != nullptr);
-    if (rc0 != IVX_OK) return rc0;
-    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
-                 reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
-                "tensors must be 16-byte aligned");
-    {
-        int perm[3] = {0, 1, 2}, mt = 1;
-        if (use_halo(p, perm, &mt))
-            return launch_conv3d_tc_halo(p, perm, mt, x, weight_bf16, scale, shift, residual, y,
-                                         (cudaStream_t)stream);
-    }
-
+// Launch of the per-tap kernel in either storage type (the bf16 entry point tries the halo kernel first).
+template <bool TF32>
+static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weight, const float *scale,
+                     const float *shift, const void *residual, void *y, void *workspace, int64_t workspace_bytes,
+                     cudaStream_t stream) {
+    constexpr int EK = TF32 ? 32 : 64;           // channels per 128-byte k-step
+    constexpr int ES = TF32 ? 4 : 2;             // bytes per element
+    constexpr int SPC = TF32 ? 2 : 1;            // 128-byte-wide slabs per 64-channel output chunk
+    // operands of the tf32 MMAs are rounded to tf32 by the TMA; outputs and residuals stay plain fp32
+    const CUtensorMapDataType dt_in = TF32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapDataType dt_out = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     TcArgs a;
     plan_tc(p, a);
     a.ws = nullptr, a.counters = nullptr;
+    const int k_steps_total = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / EK);
     if (a.k_splits > 1) {
         const long long out_tiles = a.n_tiles / a.k_splits;
         const int64_t ws_floats = out_tiles * TC_ROWS * a.n_tile;
@@ -573,33 +637,36 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
             a.n_tiles = out_tiles;
             a.k_splits = 1;
             a.div_k = make_tilediv(1);
-            a.steps_per_split = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
+            a.steps_per_split = k_steps_total;
         }
     }
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
-    a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
+    a.scale = scale, a.shift = shift, a.res = residual;
     const int32_t ones[3] = {1, 1, 1};
     const int32_t *ld_stride = p->transposed ? ones : p->stride;
     const int up_taps = p->transposed ? p->kernel[0] * p->kernel[1] * p->kernel[2] : 1;
     const int n_total = p->c_out * up_taps;
 
     const int stage_bytes = TC_A_BYTES + a.n_tile * 128;
-    const int k_steps_total = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / TC_KCHUNK);
+    const int slot_bytes = SPC * TC_A_BYTES;     // staging of one 64-channel output chunk
     const int budget = 227 * 1024 - 1024 /* barriers */ - 1024 /* alignment slack */;
-    auto stages_with = [&](int n_slabs) {
-        const int st = (budget - n_slabs * TC_A_BYTES) / stage_bytes;
+    auto stages_with = [&](int n_slots) {
+        const int st = (budget - n_slots * slot_bytes) / stage_bytes;
         return st > 8 ? 8 : st;
     };
-    // residual through TMA needs extra slabs.  A layer with few k-steps is bound by the epilogue and by
-    // the latency of the residual load, not by the main loop: give it a short pipeline and up to 8
-    // slabs (residual requested 7 chunks ahead).  Otherwise one extra slab, if 4 stages remain.
-    a.n_slabs = 2, a.res_tma = 0;
+    // Output staging: two slots, so the store of one chunk overlaps the next (one, if that buys the
+    // fourth pipeline stage).  Residual through TMA needs extra slots: a layer with few k-steps is bound
+    // by the epilogue and by the latency of the residual load, not by the main loop, so it gets a short
+    // pipeline and up to 8 slots (residual requested 7 chunks ahead); otherwise one extra slot, if 4
+    // stages remain.
+    a.n_slabs = (stages_with(2) < 4 && stages_with(1) >= 4) ? 1 : 2;
+    a.res_tma = 0;
     if (residual != nullptr && a.k_splits == 1 && !p->transposed) {
         if (k_steps_total <= 16) {
             for (int st = 4; st >= 2 && !a.res_tma; --st) {
-                int slabs = (budget - st * stage_bytes) / TC_A_BYTES;
-                if (slabs > 8) slabs = 8;
-                if (slabs >= 4) a.n_slabs = slabs, a.res_tma = 1;
+                int slots = (budget - st * stage_bytes) / slot_bytes;
+                if (slots > 8) slots = 8;
+                if (slots >= 4) a.n_slabs = slots, a.res_tma = 1;
             }
         } else if (stages_with(3) >= 4) {
             a.n_slabs = 3, a.res_tma = 1;
@@ -607,59 +674,92 @@ extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *
     }
     a.stages = stages_with(a.n_slabs);
     IVX_REQUIRE(a.stages >= 2, "not enough shared memory for a 2-stage pipeline");
-    const size_t smem = (size_t)a.stages * stage_bytes + a.n_slabs * TC_A_BYTES + 2048;
+    const size_t smem = (size_t)a.stages * stage_bytes + (size_t)a.n_slabs * slot_bytes + 2048;
 
     alignas(64) CUtensorMap map_x, map_w, map_y, map_r;
     {
         const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[2], (cuuint64_t)p->in_dims[1],
                                     (cuuint64_t)p->in_dims[0], (cuuint64_t)p->batch};
         cuuint64_t st[4];
-        st[0] = (cuuint64_t)p->c_in * 2;
+        st[0] = (cuuint64_t)p->c_in * ES;
         st[1] = st[0] * p->in_dims[2];
         st[2] = st[1] * p->in_dims[1];
         st[3] = st[2] * p->in_dims[0];
-        const cuuint32_t box[5] = {TC_KCHUNK, (cuuint32_t)(a.box[2] * ld_stride[2]),
+        const cuuint32_t box[5] = {EK, (cuuint32_t)(a.box[2] * ld_stride[2]),
                                    (cuuint32_t)(a.box[1] * ld_stride[1]), (cuuint32_t)(a.box[0] * ld_stride[0]), 1};
         const cuuint32_t es[5] = {1, (cuuint32_t)ld_stride[2], (cuuint32_t)ld_stride[1], (cuuint32_t)ld_stride[0], 1};
-        int rc = encode_map_bf16(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations");
+        int rc = encode_map_sw128(&map_x, dt_in, 5, const_cast<void *>(x), dims, st, box, es, "activations");
         if (rc != IVX_OK) return rc;
     }
     {
         // [c_out][taps * c_in] for convolutions, [taps * c_out][c_in] for transposed layers
         const int taps = p->transposed ? 1 : p->kernel[0] * p->kernel[1] * p->kernel[2];
         const cuuint64_t dims[2] = {(cuuint64_t)taps * p->c_in, (cuuint64_t)n_total};
-        const cuuint64_t st[1] = {(cuuint64_t)taps * p->c_in * 2};
-        const cuuint32_t box[2] = {TC_KCHUNK, (cuuint32_t)a.n_tile};
+        const cuuint64_t st[1] = {(cuuint64_t)taps * p->c_in * ES};
+        const cuuint32_t box[2] = {EK, (cuuint32_t)a.n_tile};
         const cuuint32_t es[2] = {1, 1};
-        int rc = encode_map_bf16(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights");
+        int rc = encode_map_sw128(&map_w, dt_in, 2, const_cast<void *>(weight), dims, st, box, es, "weights");
         if (rc != IVX_OK) return rc;
     }
     {
         const cuuint64_t dims[5] = {(cuuint64_t)p->c_out, (cuuint64_t)p->out_dims[2], (cuuint64_t)p->out_dims[1],
                                     (cuuint64_t)p->out_dims[0], (cuuint64_t)p->batch};
         cuuint64_t st[4];
-        st[0] = (cuuint64_t)p->c_out * 2;
+        st[0] = (cuuint64_t)p->c_out * ES;
         st[1] = st[0] * p->out_dims[2];
         st[2] = st[1] * p->out_dims[1];
         st[3] = st[2] * p->out_dims[0];
-        const cuuint32_t box[5] = {64, (cuuint32_t)(a.box[2] * a.up[2]), (cuuint32_t)(a.box[1] * a.up[1]),
+        const cuuint32_t box[5] = {128 / ES, (cuuint32_t)(a.box[2] * a.up[2]), (cuuint32_t)(a.box[1] * a.up[1]),
                                    (cuuint32_t)(a.box[0] * a.up[0]), 1};
         const cuuint32_t es[5] = {1, (cuuint32_t)a.up[2], (cuuint32_t)a.up[1], (cuuint32_t)a.up[0], 1};
-        int rc = encode_map_bf16(&map_y, 5, y, dims, st, box, es, "output");
+        int rc = encode_map_sw128(&map_y, dt_out, 5, y, dims, st, box, es, "output");
         if (rc != IVX_OK) return rc;
         map_r = map_y;      // the residual has the output's shape: same map over its own memory
         if (a.res_tma) {
-            rc = encode_map_bf16(&map_r, 5, const_cast<void *>(residual), dims, st, box, es, "residual");
+            rc = encode_map_sw128(&map_r, dt_out, 5, const_cast<void *>(residual), dims, st, box, es, "residual");
             if (rc != IVX_OK) return rc;
         }
     }
 
-    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_kernel<TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem),
                         "cudaFuncSetAttribute");
     if (rc != IVX_OK) return rc;
     const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
-    conv3d_tc_kernel<<<grid, TC_THREADS, smem, (cudaStream_t)stream>>>(map_x, map_w, map_y, map_r, a);
+    conv3d_tc_kernel<TF32><<<grid, TC_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
     IVX_CHECK_LAUNCH("conv3d_tc launch");
     return IVX_OK;
+}
+
+extern "C" int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *p, const void *x, const void *weight_bf16,
+                                        const float *scale, const float *shift, const void *residual,
+                                        void *y, void *workspace, int64_t workspace_bytes, void *stream) {
+    IVX_REQUIRE(p && x && weight_bf16 && y, "NULL argument");
+    int rc0 = validate_tc(p, residual != nullptr);
+    if (rc0 != IVX_OK) return rc0;
+    IVX_REQUIRE(p->in_dtype == IVX_BF16, "ivx_conv3d_ndhwc_bf16_tc takes bf16 tensors");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) |
+                 reinterpret_cast<uintptr_t>(weight_bf16) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    {
+        int perm[3] = {0, 1, 2}, mt = 1;
+        if (use_halo(p, perm, &mt))
+            return launch_conv3d_tc_halo(p, perm, mt, x, weight_bf16, scale, shift, residual, y,
+                                         (cudaStream_t)stream);
+    }
+    return launch_tc<false>(p, x, weight_bf16, scale, shift, residual, y, workspace, workspace_bytes,
+                            (cudaStream_t)stream);
+}
+
+extern "C" int ivx_conv3d_ndhwc_tf32_tc(const ivx_conv3d_params *p, const float *x, const float *weight,
+                                        const float *scale, const float *shift, const float *residual, float *y,
+                                        void *workspace, int64_t workspace_bytes, void *stream) {
+    IVX_REQUIRE(p && x && weight && y, "NULL argument");
+    int rc0 = validate_tc(p, residual != nullptr);
+    if (rc0 != IVX_OK) return rc0;
+    IVX_REQUIRE(p->in_dtype == IVX_F32, "ivx_conv3d_ndhwc_tf32_tc takes fp32 tensors");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(weight) |
+                 reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    return launch_tc<true>(p, x, weight, scale, shift, residual, y, workspace, workspace_bytes, (cudaStream_t)stream);
 }

@@ -96,6 +96,18 @@ __device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint
         : "memory");
 }
 
+// fp32 operands read as tf32 (the low 13 mantissa bits are ignored), K = 8 per instruction
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          bool accumulate) {
+    const uint32_t acc = accumulate ? 1u : 0u;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(acc)
+        : "memory");
+}
+
 // arrives on the mbarrier once every tcgen05.mma issued so far has completed
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar)
@@ -124,6 +136,14 @@ __device__ __forceinline__ uint32_t umma_idesc(int n) {
            | ((uint32_t)(128 >> 4) << 24);
 }
 
+// tf32 x tf32 -> fp32, both operands K-major, M = 128
+__device__ __forceinline__ uint32_t umma_idesc_tf32(int n) {
+    return (1u << 4)                      // accumulator format F32
+           | (2u << 7) | (2u << 10)       // A, B format TF32
+           | ((uint32_t)(n >> 3) << 17)   // N
+           | ((uint32_t)(128 >> 4) << 24);
+}
+
 // K-major operand of 128-byte rows with the 128B swizzle.  `sbo_bytes` is the distance between
 // consecutive 8-row groups.  The start address may be any 128-byte row of a box the TMA wrote
 // with the same swizzle: measured on B200, the MMA unit applies the XOR pattern to the absolute
@@ -148,5 +168,9 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t
 int encode_map_bf16(CUtensorMap *map, int rank, void *base, const cuuint64_t *dims,
                     const cuuint64_t *strides_bytes, const cuuint32_t *box, const cuuint32_t *estrides,
                     const char *what);
+// the same for any element type (fp32 tensors: FLOAT32, or TFLOAT32 for MMA operands)
+int encode_map_sw128(CUtensorMap *map, CUtensorMapDataType dtype, int rank, void *base, const cuuint64_t *dims,
+                     const cuuint64_t *strides_bytes, const cuuint32_t *box, const cuuint32_t *estrides,
+                     const char *what);
 
 }  // namespace ivx

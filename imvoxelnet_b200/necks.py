@@ -16,17 +16,23 @@ import torch
 from torch import nn
 
 from .conv import FusedConv, from_ndhwc, to_ndhwc, upsample2x_trilinear
+from .conv import tf32 as conv_tf32
 from .registry import NECKS, register
 
 __all__ = ["FastIndoorImVoxelNeck", "ImVoxelNeck", "KittiImVoxelNeck", "NuScenesImVoxelNeck"]
 
-PRECISIONS = ("fp32", "bf16")
+PRECISIONS = ("fp32", "tf32", "bf16")
 
 
 class _NeckBase(nn.Module):
     #: "fp32": fp32 activations, CUDA-core kernels, matches the reference to 1e-5.
+    #: "tf32": fp32 activations, tf32 tensor-core math (what cuDNN does for fp32 by default; 1e-3).
     #: "bf16": bf16 activations, tensor-core kernels where available (1e-2).
     precision = "fp32"
+
+    def __call__(self, *args, **kwargs):
+        with conv_tf32(self.precision == "tf32"):
+            return super().__call__(*args, **kwargs)
 
     def init_weights(self):
         pass
@@ -34,10 +40,10 @@ class _NeckBase(nn.Module):
     def _enter(self, x):
         if self.precision not in PRECISIONS:
             raise ValueError(f"precision must be one of {PRECISIONS}")
-        if self.training and torch.is_grad_enabled() and self.precision != "fp32":
+        if self.training and torch.is_grad_enabled() and self.precision == "bf16":
             raise NotImplementedError(
-                f"{type(self).__name__}: training runs in fp32 (batch-statistics BatchNorm and autograd "
-                "through the CUDA-core kernels); set precision='fp32'")
+                f"{type(self).__name__}: training keeps fp32 tensors (batch-statistics BatchNorm and autograd); "
+                "set precision='fp32' or 'tf32'")
         y = to_ndhwc(x)
         return y.to(torch.bfloat16) if self.precision == "bf16" else y.float()
 

@@ -44,6 +44,18 @@ def _moments(a, b, rows, c):
     return acc[:c], acc[c:]
 
 
+def _tf32_ok(c_in, c_out):
+    from . import conv
+    return conv._TF32 and c_in % 32 == 0 and c_out % 64 == 0
+
+
+def _conv_tf32(fc, params, x, w_tc, bias, y):
+    """y = conv(x) + bias on the tensor cores with tf32 math (weights in the tensor-core layout)."""
+    ws = fc._workspace(params, x.device)
+    _call("ivx_conv3d_ndhwc_tf32_tc", params, x.data_ptr(), w_tc.data_ptr(), None, _ptr(bias), None, y.data_ptr(),
+          ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
+
+
 def _copy_params(p, **changes):
     q = _lib.ConvParams()
     ctypes.memmove(ctypes.byref(q), ctypes.byref(p), ctypes.sizeof(q))
@@ -69,7 +81,11 @@ class _FusedLayer(torch.autograd.Function):
         wp = (w.permute(0, 2, 3, 4, 1) if fc.transposed else w.permute(2, 3, 4, 1, 0)).contiguous()
         z = torch.empty((b,) + od + (cout,), dtype=torch.float32, device=dev)
         bias_f = bias.detach().float().contiguous() if bias is not None else None
-        _call("ivx_conv3d_ndhwc", p, x.data_ptr(), wp.data_ptr(), None, _ptr(bias_f), None, z.data_ptr())
+        if _tf32_ok(cin, cout):      # precision "tf32": the convolution itself on the tensor cores
+            w_tc = (w.permute(2, 3, 4, 1, 0) if fc.transposed else w.permute(0, 2, 3, 4, 1)).contiguous()
+            _conv_tf32(fc, p, x, w_tc, bias_f, z)
+        else:
+            _call("ivx_conv3d_ndhwc", p, x.data_ptr(), wp.data_ptr(), None, _ptr(bias_f), None, z.data_ptr())
         rows = z.numel() // cout
         sc = sh = mean = invstd = None
         batch_stats = bn is not None and bn.training
@@ -145,11 +161,22 @@ class _FusedLayer(torch.autograd.Function):
         dx = None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x)
+            unit_stride = all(p.stride[d] == 1 for d in range(3))
             if fc.transposed:    # data gradient of a kernel == stride transposed conv: a plain strided conv of dz
                 q = _copy_params(p, c_in=cout, c_out=cin, in_dims=tuple(p.out_dims), out_dims=tuple(p.in_dims),
-                                 transposed=0)
-                wt = wp.permute(1, 2, 3, 4, 0).contiguous()        # [Cin,k,k,k,Cout] -> [taps][Cout][Cin]
-                _call("ivx_conv3d_ndhwc", q, dz.data_ptr(), wt.data_ptr(), None, None, None, dx.data_ptr())
+                                 transposed=0, relu=0, residual_after_act=0, post_scale=1.0)
+                if _tf32_ok(cout, cin):
+                    _conv_tf32(fc, q, dz, wp.contiguous(), None, dx)   # wp is [Cin][k][k][k][Cout] already
+                else:
+                    wt = wp.permute(1, 2, 3, 4, 0).contiguous()    # [Cin,k,k,k,Cout] -> [taps][Cout][Cin]
+                    _call("ivx_conv3d_ndhwc", q, dz.data_ptr(), wt.data_ptr(), None, None, None, dx.data_ptr())
+            elif unit_stride and _tf32_ok(cout, cin):
+                # stride 1: the data gradient is the convolution of dz with the flipped, transposed kernel
+                q = _copy_params(p, c_in=cout, c_out=cin, in_dims=tuple(p.out_dims), out_dims=tuple(p.in_dims),
+                                 pad=tuple(p.kernel[d] - 1 - p.pad[d] for d in range(3)), relu=0,
+                                 residual_after_act=0, post_scale=1.0)
+                w_flip = wp.flip(0, 1, 2).permute(3, 0, 1, 2, 4).contiguous()   # [k][k][k][Cin][Cout] -> [Cin][k'][Cout]
+                _conv_tf32(fc, q, dz, w_flip, None, dx)
             else:
                 wt = wp.permute(0, 1, 2, 4, 3).contiguous()        # [taps][Cin][Cout] -> [taps][Cout][Cin]
                 _call("ivx_conv3d_dgrad_ndhwc", p, dz.data_ptr(), wt.data_ptr(), dx.data_ptr())
@@ -162,7 +189,7 @@ class _FusedLayer(torch.autograd.Function):
 def fused_layer_train(fc, x, residual=None, residual_after_act=False, post_scale=1.0):
     """Differentiable forward of a ``FusedConv`` (fp32 channels-last tensors)."""
     if x.dtype != torch.float32:
-        raise NotImplementedError("training runs in fp32: set precision='fp32' on the neck")
+        raise NotImplementedError("training keeps fp32 tensors: set precision='fp32' or 'tf32' on the neck")
     bn = fc.bn
     return _FusedLayer.apply(x.contiguous(), fc.conv.weight, fc.conv.bias,
                              bn.weight if bn is not None else None, bn.bias if bn is not None else None,

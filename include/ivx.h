@@ -358,6 +358,21 @@ IVX_API int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *params, const void
                                      int64_t workspace_bytes, void *stream);
 
 /*
+ * ivx_conv3d_ndhwc_tf32_tc -- the same kernel for fp32 tensors with tf32 math
+ * (tcgen05.mma kind::tf32: 10-bit mantissa operands, rounded by the TMA, fp32
+ * accumulation): what PyTorch / cuDNN do for fp32 convolutions by default on
+ * this hardware (torch.backends.cudnn.allow_tf32).  About 1e-3 of the fp32
+ * result: a third precision between the 1e-5 CUDA-core path and bf16.
+ * x, y, residual: fp32 channels-last; weight: fp32 in the layout of
+ * ivx_conv3d_ndhwc_bf16_tc; c_in % 32 == 0, c_out % 64 == 0; workspace as
+ * above (ivx_conv3d_tc_workspace_bytes with in_dtype = out_dtype = IVX_F32).
+ * Used by the "tf32" precision of the necks and by the training path.
+ */
+IVX_API int ivx_conv3d_ndhwc_tf32_tc(const ivx_conv3d_params *params, const float *x, const float *weight,
+                                     const float *scale, const float *shift, const float *residual, float *y,
+                                     void *workspace, int64_t workspace_bytes, void *stream);
+
+/*
  * ivx_upsample2x_trilinear_ndhwc -- F.interpolate(x, scale_factor=2,
  * mode='trilinear', align_corners=False) of EncoderDecoder.forward
  * (necks/imvoxelnet.py:359) on a channels-last [batch][X][Y][Z][C] tensor;

@@ -58,6 +58,7 @@ def main():
         ref = torch_necks.NECKS[args.neck](**kw).to(dev).train()
         mine = getattr(necks, args.neck)(**kw).to(dev).train()
         mine.load_state_dict(ref.state_dict())
+        mine.precision = args.precision if args.precision in ("fp32", "tf32") else "fp32"
         x = torch.randn((args.batch,) + shape, device=dev).contiguous(memory_format=torch.channels_last_3d)
 
         def step(m, inp):
@@ -65,7 +66,7 @@ def main():
             xin = inp.clone().requires_grad_(True)
             sum(o.float().square().mean() for o in m(xin)).backward()
 
-        out = {"neck": args.neck, "batch": args.batch, "mode": "train fwd+bwd, fp32"}
+        out = {"neck": args.neck, "batch": args.batch, "mode": "train fwd+bwd, " + mine.precision}
         out["ours_ms"] = timed(lambda: step(mine, x), reps=3, warm=1)
         out["torch_cudnn_fp32_ms"] = timed(lambda: step(ref, x.contiguous()), reps=3, warm=1)
         torch.backends.cudnn.allow_tf32 = True
@@ -78,6 +79,7 @@ def main():
     x = torch.randn((args.batch,) + shape, device=dev).contiguous(memory_format=torch.channels_last_3d)
     if args.precision == "bf16":
         x = x.to(torch.bfloat16)
+    # (fp32 and tf32 keep fp32 tensors)
     out = {"neck": args.neck, "batch": args.batch, "precision": args.precision}
     if args.layers:
         records = {}
