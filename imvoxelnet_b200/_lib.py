@@ -87,6 +87,8 @@ PROTOTYPES["ivx_resize_mask_trilinear"] = [c_void_p, c_int, c_int, _i32p, _i32p,
 PROTOTYPES["ivx_head_scores"] = [c_void_p, c_void_p, c_void_p, c_int, c_int64, c_int, c_void_p, c_void_p,
                                  c_void_p]
 PROTOTYPES["ivx_compute_projection"] = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]
+PROTOTYPES["ivx_conv3d_wgrad_tf32_axes"] = [_ConvP, _i32p]
+PROTOTYPES["ivx_conv3d_wgrad_tf32_tc"] = [_ConvP, c_void_p, _i64p, c_void_p, _i64p, c_void_p, c_void_p]
 RESTYPES = {"ivx_backproject_nchw_workspace_bytes": c_int64, "ivx_conv3d_tc_workspace_bytes": c_int64}
 
 _lib = None

@@ -1,0 +1,282 @@
+// Weight gradient of a Conv3d layer on tcgen05 (tf32 math), training mode.
+//
+//   dW[tap][co][ci] = sum over output voxels o of  dz[o][co] * x[o * stride - pad + tap][ci]
+//
+// is, per tap, a GEMM whose reduction runs over VOXELS.  tcgen05 wants both operands K-major in
+// shared memory, i.e. voxels contiguous: the caller hands in channel-major ("transposed") copies
+//   dz_t [batch][c_out][D2][D1][D0]     x_t [batch][c_in][I2][I1][I0]      (fp32, D0 fastest)
+// where (D0, D1, D2) is a permutation of the layer's (X, Y, Z) chosen so that the innermost axis has
+// stride 1 (the TMA cannot stride its innermost dimension); rows may be padded (pitches are given).
+// The TMA also wants the innermost coordinate of a swizzled box 16-byte aligned (measured: an x box
+// starting one voxel to the left is an illegal instruction), so the tap shift along the innermost axis
+// cannot be a coordinate: x_t holds one copy per tap position along that axis, already shifted,
+//   x_t [k0][batch][c_in][I2][I1][D0]     x_t[j][..][o] = x[..][o - pad0 + j]   (0 outside)
+// and tap t0 reads copy t0 at the output coordinate itself.
+// A k-step is a run of 32 output voxels along D0: one 5-D TMA box load per operand puts
+// [channel rows][32 voxels] = [rows][128 bytes] tiles into shared memory, 128B-swizzled -- the same
+// K-major layout the forward kernel feeds to the MMA.  The x box starts at o * stride - pad + tap with
+// the layer stride as the TMA's element stride, so padding and ragged borders are the TMA's zero fill.
+// One CTA owns (tap, 128 output channels, up to 256 input channels, a slice of the voxel range):
+// warp 0 issues the loads, warp 1 the MMAs (M = 128 rows of c_out, N = c_in tile, K = 8 per
+// instruction, fp32 accumulator in TMEM), warps 2..5 add the accumulator into dW with 128-bit
+// vector reductions when the slice is done (dW must be zero-filled by the caller).
+#include "ivx_tc_ptx.cuh"
+
+namespace ivx {
+
+constexpr int WG_THREADS = 192;      // warp 0: TMA, warp 1: MMA, warps 2..5: epilogue
+constexpr int WG_A_BYTES = 128 * 128;
+
+struct WgArgs {
+    int c_in, c_out, n_tile;         // n_tile: input channels per CTA tile
+    int ci_tiles, co_tiles;
+    int kernel[3], stride[3], pad[3];   // in the permuted axis order (index 0 = innermost)
+    int orig_axis[3];                // permuted axis i is axis orig_axis[i] of (X, Y, Z)
+    int orig_kernel[3];              // kernel sizes along X, Y, Z
+    int box[3], chunks[3], batch;    // voxels per k-step along each permuted axis, k-steps per axis
+    long long k_steps;               // batch * chunks[0] * chunks[1] * chunks[2]
+    int k_splits;
+    long long steps_per_split;
+    int stages;
+    int a_rows;                      // rows of the grad_z box: min(c_out, 128)
+    int debug;                       // IVX_WG_DEBUG bits: 1 no TMA loads, 2 no MMAs, 4 no epilogue reads
+    float *dw;                       // [taps (kx,ky,kz order)][c_out][c_in]
+    TileDiv div_split, div_ci, div_co, div_c0, div_c1, div_c2;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_constant__ CUtensorMap map_x,
+                       const __grid_constant__ WgArgs a) {
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    const int b_bytes = a.n_tile * 128;
+    const int stage_bytes = WG_A_BYTES + b_bytes;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)a.stages * stage_bytes);
+    uint64_t *full_bar = bars, *empty_bar = bars + a.stages, *acc_full = bars + 2 * a.stages;
+    uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tmem_cols = a.n_tile <= 32 ? 32 : (a.n_tile <= 64 ? 64 : (a.n_tile <= 128 ? 128 : 256));
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < a.stages; ++s) {
+            mbar_init(smem_u32(full_bar + s), 1);
+            mbar_init(smem_u32(empty_bar + s), 1);
+        }
+        mbar_init(smem_u32(acc_full), 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_dz) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
+    }
+    if (warp == 1) tmem_alloc(smem_u32(tmem_slot), tmem_cols);
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    // work item of this CTA: (k-slice, c_in tile, c_out tile, tap)
+    int item = blockIdx.x, split, ci_t, co_t;
+    item = a.div_split.divmod(item, split);
+    item = a.div_ci.divmod(item, ci_t);
+    const int tap_p = a.div_co.divmod(item, co_t);          // tap index in permuted-axis order
+    const int t0 = tap_p % a.kernel[0], t1 = (tap_p / a.kernel[0]) % a.kernel[1], t2 = tap_p / (a.kernel[0] * a.kernel[1]);
+    const long long k_lo = (long long)split * a.steps_per_split;
+    const long long k_hi = k_lo + a.steps_per_split < a.k_steps ? k_lo + a.steps_per_split : a.k_steps;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            uint32_t stage = 0, phase = 0;
+            for (long long ks = k_lo; ks < k_hi; ++ks) {
+                int r0, r1, r2;
+                int t = a.div_c0.divmod((int)ks, r0);
+                t = a.div_c1.divmod(t, r1);
+                const int b = a.div_c2.divmod(t, r2);
+                const int o0 = r0 * a.box[0], o1 = r1 * a.box[1], o2 = r2 * a.box[2];
+                mbar_wait(smem_u32(empty_bar + stage), phase ^ 1);
+                const uint32_t bar = smem_u32(full_bar + stage);
+                const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+                if (a.debug & 1) {
+                    mbar_arrive(bar);
+                } else {
+                    // a box always arrives in full, whatever part of it lies outside the tensor
+                    mbar_expect_tx(bar, (uint32_t)(((a.debug & 8) ? 0 : a.a_rows * 128) + ((a.debug & 16) ? 0 : b_bytes)));
+                    if (!(a.debug & 8)) tma_load_5d(sa, &map_dz, bar, o0, o1, o2, co_t * 128, b);
+                    if (!(a.debug & 16))
+                        tma_load_5d(sa + WG_A_BYTES, &map_x, bar, o0, o1 * a.stride[1] - a.pad[1] + t1,
+                                    o2 * a.stride[2] - a.pad[2] + t2, ci_t * a.n_tile, t0 * a.batch + b);
+                }
+                if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_tf32(a.n_tile);
+            uint32_t stage = 0, phase = 0;
+            for (long long ks = k_lo; ks < k_hi; ++ks) {
+                mbar_wait(smem_u32(full_bar + stage), phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
+                const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + WG_A_BYTES);
+#pragma unroll
+                for (int k = 0; k < 4; ++k)   // 8 voxels (32 bytes) per MMA inside the 128-byte row
+                    if (!(a.debug & 2)) umma_tf32(tmem_base, da + 2 * k, db + 2 * k, idesc, (ks > k_lo) || k != 0);
+                umma_commit(smem_u32(empty_bar + stage));
+                if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
+            }
+            umma_commit(smem_u32(acc_full));
+        }
+    } else if (k_hi > k_lo) {
+        // epilogue: lane = output channel of the tile, columns = input channels
+        const int q = warp & 3;
+        const int co = co_t * 128 + q * 32 + lane;
+        // tap index in the (kx, ky, kz) order of the weight tensor
+        int k3[3];
+        k3[a.orig_axis[0]] = t0, k3[a.orig_axis[1]] = t1, k3[a.orig_axis[2]] = t2;
+        const int tap = (k3[0] * a.orig_kernel[1] + k3[1]) * a.orig_kernel[2] + k3[2];
+        float *dst = a.dw + ((long long)tap * a.c_out + co) * a.c_in + ci_t * a.n_tile;
+        mbar_wait(smem_u32(acc_full), 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        for (int c = 0; c < ((a.debug & 4) ? 0 : a.n_tile); c += 32) {
+            uint32_t v[32];
+            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c, v);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            if (co < a.c_out) {
+#pragma unroll
+                for (int j = 0; j < 32; j += 4)
+                    if (c + j < a.n_tile)
+                        atomicAdd(reinterpret_cast<float4 *>(dst + c + j),
+                                  make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                              __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+            }
+        }
+    }
+
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+}  // namespace ivx
+
+using namespace ivx;
+
+// Plan shared by the entry point and the layout query: which axis goes innermost.  A k-step is a run
+// of 32 voxels along that axis (one full 128-byte swizzle row per channel: boxes with a shorter inner
+// dimension are refused by the TMA in this mode -- measured -- so a short axis is padded by the
+// zero fill instead).  Candidates are the stride-1 axes; the one wasting the fewest voxels wins,
+// ties go to the tensor's own fastest axis (Z).
+static int plan_wgrad(const ivx_conv3d_params *p, int axis[3], int box[3]) {
+    int inner = -1;
+    double best = -1.0;
+    for (int d = 2; d >= 0; --d) {
+        if (p->stride[d] != 1) continue;
+        const int n = p->out_dims[d];
+        const double eff = (double)n / (double)(((n + 31) / 32) * 32);
+        if (eff > best + 1e-9) best = eff, inner = d;
+    }
+    if (inner < 0) return -1;
+    axis[0] = inner;
+    int n = 1;
+    for (int d = 2; d >= 0; --d)
+        if (d != inner) axis[n++] = d;
+    box[0] = 32, box[1] = 1, box[2] = 1;
+    return 0;
+}
+
+extern "C" int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *p, int32_t *axes /* host[3] */) {
+    IVX_REQUIRE(p && axes, "NULL argument");
+    if (p->transposed || p->c_in % 32 != 0 || p->c_out % 32 != 0)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core weight gradient: plain convolutions with c_in, c_out multiples of 32");
+    int axis[3], box[3];
+    if (plan_wgrad(p, axis, box) != 0)
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core weight gradient: at least one axis must have stride 1");
+    for (int i = 0; i < 3; ++i) axes[i] = axis[i];
+    return IVX_OK;
+}
+
+extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float *x_t, const int64_t *x_pitch,
+                                        const float *dz_t, const int64_t *dz_pitch, float *grad_w, void *stream) {
+    IVX_REQUIRE(p && x_t && dz_t && grad_w && x_pitch && dz_pitch, "NULL argument");
+    int32_t axes[3];
+    int rc = ivx_conv3d_wgrad_tf32_axes(p, axes);
+    if (rc != IVX_OK) return rc;
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x_t) | reinterpret_cast<uintptr_t>(dz_t) |
+                 reinterpret_cast<uintptr_t>(grad_w)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    for (int i = 0; i < 4; ++i)
+        IVX_REQUIRE(x_pitch[i] > 0 && dz_pitch[i] > 0 && x_pitch[i] % 4 == 0 && dz_pitch[i] % 4 == 0,
+                    "pitches must be positive multiples of 4 elements (16 bytes)");
+    WgArgs a;
+    int axis[3];
+    plan_wgrad(p, axis, a.box);
+    a.c_in = p->c_in, a.c_out = p->c_out;
+    a.n_tile = p->c_in % 256 == 0 ? 256 : (p->c_in % 128 == 0 ? 128 : (p->c_in % 64 == 0 ? 64 : 32));
+    a.ci_tiles = p->c_in / a.n_tile;
+    a.co_tiles = (p->c_out + 127) / 128;
+    a.batch = p->batch;
+    long long k_steps = p->batch;
+    for (int i = 0; i < 3; ++i) {
+        a.kernel[i] = p->kernel[axis[i]], a.stride[i] = p->stride[axis[i]], a.pad[i] = p->pad[axis[i]];
+        a.orig_axis[i] = axis[i], a.orig_kernel[i] = p->kernel[i];
+        a.chunks[i] = (p->out_dims[axis[i]] + a.box[i] - 1) / a.box[i];
+        k_steps *= a.chunks[i];
+    }
+    IVX_REQUIRE(k_steps < (1ll << 31), "too many voxels");
+    a.k_steps = k_steps;
+    const int n_taps = p->kernel[0] * p->kernel[1] * p->kernel[2];
+    const long long tiles = (long long)n_taps * a.co_tiles * a.ci_tiles;
+    // enough k-slices to fill the GPU a few times over, at least 64 k-steps each
+    long long splits = (4ll * kNumSMs + tiles - 1) / tiles;
+    if (splits > k_steps / 64) splits = k_steps / 64;
+    if (splits < 1) splits = 1;
+    a.steps_per_split = (k_steps + splits - 1) / splits;
+    a.k_splits = (int)((k_steps + a.steps_per_split - 1) / a.steps_per_split);
+    IVX_REQUIRE(tiles * a.k_splits < (1ll << 31), "too many work items");
+    a.dw = grad_w;
+    a.a_rows = p->c_out < 128 ? p->c_out : 128;
+    {
+        const char *e = getenv("IVX_WG_DEBUG");
+        a.debug = e ? atoi(e) : 0;
+    }
+    a.div_split = make_tilediv(a.k_splits), a.div_ci = make_tilediv(a.ci_tiles), a.div_co = make_tilediv(a.co_tiles);
+    a.div_c0 = make_tilediv(a.chunks[0]), a.div_c1 = make_tilediv(a.chunks[1]), a.div_c2 = make_tilediv(a.chunks[2]);
+    const int stage_bytes = WG_A_BYTES + a.n_tile * 128;
+    a.stages = (227 * 1024 - 2048) / stage_bytes;
+    if (a.stages > 8) a.stages = 8;
+    const size_t smem = (size_t)a.stages * stage_bytes + 2048;
+
+    alignas(64) CUtensorMap map_dz, map_x;
+    {
+        const cuuint64_t dims[5] = {(cuuint64_t)p->out_dims[axis[0]], (cuuint64_t)p->out_dims[axis[1]],
+                                    (cuuint64_t)p->out_dims[axis[2]], (cuuint64_t)p->c_out, (cuuint64_t)p->batch};
+        const cuuint64_t st[4] = {(cuuint64_t)dz_pitch[0] * 4, (cuuint64_t)dz_pitch[1] * 4, (cuuint64_t)dz_pitch[2] * 4,
+                                  (cuuint64_t)dz_pitch[3] * 4};
+        const cuuint32_t box[5] = {(cuuint32_t)a.box[0], (cuuint32_t)a.box[1], (cuuint32_t)a.box[2],
+                                   (cuuint32_t)(p->c_out < 128 ? p->c_out : 128), 1};
+        const cuuint32_t es[5] = {1, 1, 1, 1, 1};
+        rc = encode_map_sw128(&map_dz, (a.debug & 32) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 5, const_cast<float *>(dz_t), dims, st, box,
+                              es, "grad_z (channel-major)");
+        if (rc != IVX_OK) return rc;
+    }
+    {
+        // innermost: the OUTPUT extent (the copies are indexed by output coordinate); outermost: copy x batch
+        const cuuint64_t dims[5] = {(cuuint64_t)p->out_dims[axis[0]], (cuuint64_t)p->in_dims[axis[1]],
+                                    (cuuint64_t)p->in_dims[axis[2]], (cuuint64_t)p->c_in,
+                                    (cuuint64_t)p->batch * p->kernel[axis[0]]};
+        const cuuint64_t st[4] = {(cuuint64_t)x_pitch[0] * 4, (cuuint64_t)x_pitch[1] * 4, (cuuint64_t)x_pitch[2] * 4,
+                                  (cuuint64_t)x_pitch[3] * 4};
+        const cuuint32_t box[5] = {(cuuint32_t)a.box[0], (cuuint32_t)(a.box[1] * a.stride[1]),
+                                   (cuuint32_t)(a.box[2] * a.stride[2]), (cuuint32_t)a.n_tile, 1};
+        const cuuint32_t es[5] = {1, (cuuint32_t)a.stride[1], (cuuint32_t)a.stride[2], 1, 1};
+        rc = encode_map_sw128(&map_x, (a.debug & 32) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 5, const_cast<float *>(x_t), dims, st, box, es,
+                              "x (channel-major)");
+        if (rc != IVX_OK) return rc;
+    }
+    rc = check_cuda(cudaFuncSetAttribute(conv3d_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)smem),
+                    "cudaFuncSetAttribute");
+    if (rc != IVX_OK) return rc;
+    conv3d_wgrad_tc_kernel<<<(unsigned)(tiles * a.k_splits), WG_THREADS, smem, (cudaStream_t)stream>>>(map_dz, map_x, a);
+    IVX_CHECK_LAUNCH("conv3d wgrad (tensor cores) launch");
+    return IVX_OK;
+}

@@ -31,10 +31,22 @@ def _ptr(t):
     return t.data_ptr() if t is not None else None
 
 
+PROFILE = None      # set to a dict to collect {entry point: [calls, device ms]} (synchronises every call)
+
+
 def _call(name, *args):
     global _launches
+    if PROFILE is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     _lib.check(getattr(_lib.lib(), name)(*args, _stream()), name)
     _launches += 1
+    if PROFILE is not None:
+        e1.record()
+        torch.cuda.synchronize()
+        rec = PROFILE.setdefault(name, [0, 0.0])
+        rec[0] += 1
+        rec[1] += e0.elapsed_time(e1)
 
 
 def _moments(a, b, rows, c):
@@ -54,6 +66,50 @@ def _conv_tf32(fc, params, x, w_tc, bias, y):
     ws = fc._workspace(params, x.device)
     _call("ivx_conv3d_ndhwc_tf32_tc", params, x.data_ptr(), w_tc.data_ptr(), None, _ptr(bias), None, y.data_ptr(),
           ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
+
+
+def _channel_major(t, axes, shifts=None, out_len=None):
+    """[B, X, Y, Z, C] -> dense [B, C, D2, D1, D0p] with D_i = axis axes[i], rows padded to 4 elements, and
+    the element pitches of dimensions 1..4 (what ivx_conv3d_wgrad_tf32_tc takes).  With ``shifts`` the
+    result is [len(shifts), B, C, D2, D1, Lp]: copy j holds ``t[.., o + shifts[j]]`` at ``o < out_len``
+    (zero outside the volume)."""
+    v = t.permute(0, 4, 1 + axes[2], 1 + axes[1], 1 + axes[0])
+    d0 = v.shape[-1]
+    if shifts is None:
+        d0p = -(-d0 // 4) * 4
+        if d0p == d0:
+            out = v.contiguous()
+        else:
+            out = torch.zeros(tuple(v.shape[:-1]) + (d0p,), dtype=t.dtype, device=t.device)
+            out[..., :d0].copy_(v)
+    else:
+        d0p = -(-out_len // 4) * 4
+        out = torch.zeros((len(shifts),) + tuple(v.shape[:-1]) + (d0p,), dtype=t.dtype, device=t.device)
+        for j, s in enumerate(shifts):
+            lo, hi = max(0, -s), min(out_len, d0 - s)
+            if hi > lo:
+                out[j, ..., lo:hi].copy_(v[..., lo + s:hi + s])
+    c, d2, d1 = out.shape[-4], out.shape[-3], out.shape[-2]
+    return out, _lib.i64([d0p, d0p * d1, d0p * d1 * d2, c * d0p * d1 * d2])
+
+
+def _wgrad_tf32(p, x, dz):
+    """Weight gradient on the tensor cores, or None when the layer is not one it takes."""
+    from . import conv
+    if not conv._TF32 or p.transposed or p.c_in % 32 or p.c_out % 32:
+        return None
+    axes = _lib.i32([0, 0, 0])
+    if _lib.lib().ivx_conv3d_wgrad_tf32_axes(p, axes) != 0:
+        return None
+    axes = list(axes)
+    a0 = axes[0]        # innermost axis: its tap shift is baked into one copy of x per tap position
+    x_t, x_pitch = _channel_major(x, axes, shifts=[j - p.pad[a0] for j in range(p.kernel[a0])],
+                                  out_len=p.out_dims[a0])
+    dz_t, dz_pitch = _channel_major(dz, axes)
+    k = tuple(p.kernel)
+    dw = torch.zeros((k[0], k[1], k[2], p.c_out, p.c_in), dtype=torch.float32, device=x.device)
+    _call("ivx_conv3d_wgrad_tf32_tc", p, x_t.data_ptr(), x_pitch, dz_t.data_ptr(), dz_pitch, dw.data_ptr())
+    return dw.permute(3, 4, 0, 1, 2)        # torch's [Cout, Cin, kX, kY, kZ]
 
 
 def _copy_params(p, **changes):
@@ -113,6 +169,8 @@ class _FusedLayer(torch.autograd.Function):
             y = torch.empty_like(z)
             _call("ivx_affine_act_ndhwc", z.data_ptr(), _ptr(sc), _ptr(sh), _ptr(residual), int(fc.relu),
                   int(after), float(post), rows, cout, y.data_ptr())
+        from . import conv as _conv
+        ctx.tf32 = _conv._TF32       # the backward pass runs outside the neck's tf32 context: remember it
         ctx.fc, ctx.p, ctx.flags = fc, p, (after, post, trivial, batch_stats, rows)
         ctx.has_bias = bias is not None
         keep_res = residual if (residual is not None and fc.relu and not after) else None
@@ -122,6 +180,12 @@ class _FusedLayer(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, dy):
+        from . import conv as _conv
+        with _conv.tf32(ctx.tf32):
+            return _FusedLayer._backward(ctx, dy)
+
+    @staticmethod
+    def _backward(ctx, dy):
         fc, p = ctx.fc, ctx.p
         after, post, trivial, batch_stats, rows = ctx.flags
         x, wp, z, sc, sh, mean, invstd, res = ctx.saved_tensors
@@ -180,9 +244,11 @@ class _FusedLayer(torch.autograd.Function):
             else:
                 wt = wp.permute(0, 1, 2, 4, 3).contiguous()        # [taps][Cin][Cout] -> [taps][Cout][Cin]
                 _call("ivx_conv3d_dgrad_ndhwc", p, dz.data_ptr(), wt.data_ptr(), dx.data_ptr())
-        dwp = torch.zeros_like(wp)
-        _call("ivx_conv3d_wgrad_ndhwc", p, x.data_ptr(), dz.data_ptr(), dwp.data_ptr())
-        dw = dwp.permute(0, 4, 1, 2, 3) if fc.transposed else dwp.permute(4, 3, 0, 1, 2)
+        dw = _wgrad_tf32(p, x, dz)
+        if dw is None:
+            dwp = torch.zeros_like(wp)
+            _call("ivx_conv3d_wgrad_ndhwc", p, x.data_ptr(), dz.data_ptr(), dwp.data_ptr())
+            dw = dwp.permute(0, 4, 1, 2, 3) if fc.transposed else dwp.permute(4, 3, 0, 1, 2)
         return dx, dw.contiguous(), dbias, dgamma, dbeta, dres, None, None, None
 
 

@@ -431,6 +431,28 @@ IVX_API int ivx_conv3d_dgrad_ndhwc(const ivx_conv3d_params *params, const float 
 IVX_API int ivx_conv3d_wgrad_ndhwc(const ivx_conv3d_params *params, const float *x, const float *grad_z,
                                    float *grad_w, void *stream);
 
+/*
+ * ivx_conv3d_wgrad_tf32_tc -- the weight gradient on the tensor cores (tf32 math), for plain
+ * convolutions with c_in, c_out multiples of 32 and stride 1 along at least one axis:
+ *   grad_w[tap][c_out][c_in] += sum_o grad_z[o][c_out] * x[o * stride - pad + tap][c_in]
+ * (taps in kX, kY, kZ order; grad_w fp32, zero-filled by the caller; fp32 vector reductions).
+ * The reduction runs over voxels, so both operands are taken CHANNEL-MAJOR:
+ *   dz_t [batch][c_out][D2][D1][D0]      x_t [k0][batch][c_in][I2][I1][D0]
+ * where permuted axis i is axis axes[i] of (X, Y, Z) as returned by ivx_conv3d_wgrad_tf32_axes
+ * (axes[0], the innermost, always has stride 1), D = out_dims and I = in_dims in that order,
+ * and k0 = kernel[axes[0]].  x_t holds one copy of x per tap position along the innermost axis,
+ * already shifted:  x_t[j][..][o] = x[..][o - pad[axes[0]] + j], zero outside the volume (the TMA
+ * cannot start a swizzled box at an unaligned innermost coordinate, so that shift cannot be a
+ * coordinate; the shifts along the other two axes are).  x_pitch / dz_pitch: host[4], element
+ * pitches of dimensions 1..4 (row, plane, channel, batch), multiples of 4 -- rows may be padded;
+ * the copies of x_t follow each other at batch * x_pitch[3].
+ * IVX_ERR_UNSUPPORTED for other layers (callers use ivx_conv3d_wgrad_ndhwc).
+ */
+IVX_API int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *params, int32_t *axes /* host[3] */);
+IVX_API int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *params, const float *x_t,
+                                     const int64_t *x_pitch /* host[4] */, const float *dz_t,
+                                     const int64_t *dz_pitch /* host[4] */, float *grad_w, void *stream);
+
 /* grad_x [batch][X][Y][Z][C] += transpose of ivx_upsample2x_trilinear_ndhwc applied to grad_y
  * [batch][2X][2Y][2Z][C]; grad_x must be zero-filled by the caller */
 IVX_API int ivx_upsample2x_trilinear_backward_ndhwc(const float *grad_y, float *grad_x, int batch,

@@ -131,7 +131,9 @@ def test_neck_in_tf32_precision(name):
 
 @pytest.mark.parametrize("kind,cin,cout,dims", [("k3", 64, 64, (6, 7, 5)), ("k3", 128, 64, (5, 4, 6)),
                                                 ("k1", 64, 128, (4, 4, 4)), ("k3s2", 64, 128, (8, 6, 4)),
-                                                ("up", 128, 64, (3, 4, 2)), ("k3p0", 64, 64, (6, 6, 3))])
+                                                ("up", 128, 64, (3, 4, 2)), ("k3p0", 64, 64, (6, 6, 3)),
+                                                ("k3sz", 64, 128, (6, 9, 6)), ("k3sz", 128, 256, (5, 8, 3)),
+                                                ("k3", 32, 96, (9, 4, 10)), ("k3", 256, 256, (4, 4, 4))])
 def test_single_layer_gradients_in_tf32(kind, cin, cout, dims):
     """One fused layer (conv + batch-statistics BN, no activation: a ReLU mask flipped by the tf32 forward would
     dominate the comparison) differentiated with the forward and the data gradient on the tensor cores
@@ -141,7 +143,8 @@ def test_single_layer_gradients_in_tf32(kind, cin, cout, dims):
     if kind == "up":
         layer = nn.ConvTranspose3d(cin, cout, 2, 2, bias=False).to(DEV)
     else:
-        k, s, p = {"k3": (3, 1, 1), "k1": (1, 1, 0), "k3s2": (3, 2, 1), "k3p0": (3, 1, 0)}[kind]
+        k, s, p = {"k3": (3, 1, 1), "k1": (1, 1, 0), "k3s2": (3, 2, 1), "k3p0": (3, 1, 0),
+                   "k3sz": (3, (1, 1, 2), 1)}[kind]
         layer = nn.Conv3d(cin, cout, k, s, p, bias=False).to(DEV)
     bn = nn.BatchNorm3d(cout).to(DEV).train()
     with torch.no_grad():

@@ -68,6 +68,16 @@ def main():
 
         out = {"neck": args.neck, "batch": args.batch, "mode": "train fwd+bwd, " + mine.precision}
         out["ours_ms"] = timed(lambda: step(mine, x), reps=3, warm=1)
+        from imvoxelnet_b200 import train
+        train.PROFILE = {}
+        t0 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0[0].record()
+        step(mine, x)
+        t0[1].record()
+        torch.cuda.synchronize()
+        out["profiled_step_ms"] = t0[0].elapsed_time(t0[1])
+        out["kernel_ms"] = {k: [v[0], round(v[1], 2)] for k, v in sorted(train.PROFILE.items(), key=lambda kv: -kv[1][1])}
+        train.PROFILE = None
         out["torch_cudnn_fp32_ms"] = timed(lambda: step(ref, x.contiguous()), reps=3, warm=1)
         torch.backends.cudnn.allow_tf32 = True
         out["torch_cudnn_tf32_ms"] = timed(lambda: step(ref, x.contiguous()), reps=3, warm=1)
