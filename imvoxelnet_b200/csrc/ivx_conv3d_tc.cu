@@ -509,7 +509,7 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
 
 using namespace ivx;
 
-static int validate_tc(const ivx_conv3d_params *p, bool has_residual) {
+static int validate_tc(const ivx_conv3d_params *p, bool has_residual, bool free_output = false) {
     IVX_REQUIRE(p != nullptr, "NULL params");
     const bool bf16 = p->in_dtype == IVX_BF16 && p->out_dtype == IVX_BF16;
     const bool tf32 = p->in_dtype == IVX_F32 && p->out_dtype == IVX_F32;
@@ -524,7 +524,7 @@ static int validate_tc(const ivx_conv3d_params *p, bool has_residual) {
         const int expect = p->transposed ? p->in_dims[d] * p->stride[d]
                                          : (p->in_dims[d] + 2 * p->pad[d] - p->kernel[d]) / p->stride[d] + 1;
         IVX_REQUIRE(p->kernel[d] >= 1 && p->stride[d] >= 1 && p->stride[d] <= 8 && p->pad[d] >= 0 &&
-                        expect == p->out_dims[d] && p->out_dims[d] > 0,
+                        (expect == p->out_dims[d] || free_output) && p->out_dims[d] > 0,
                     "bad geometry on axis %d", d);
         if (p->transposed)
             IVX_REQUIRE(p->kernel[d] == p->stride[d] && p->pad[d] == 0,
@@ -600,7 +600,7 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
 }
 
 extern "C" int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *p) {
-    if (validate_tc(p, false) != IVX_OK) return 0;
+    if (validate_tc(p, false, true) != IVX_OK) return 0;
     int perm[3] = {0, 1, 2}, mt = 1;
     if (use_halo(p, perm, &mt)) return 0;
     TcArgs a;
@@ -614,7 +614,7 @@ extern "C" int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *p) {
 template <bool TF32>
 static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weight, const float *scale,
                      const float *shift, const void *residual, void *y, void *workspace, int64_t workspace_bytes,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, const int64_t *y_strides = nullptr) {
     constexpr int EK = TF32 ? 32 : 64;           // channels per 128-byte k-step
     constexpr int ES = TF32 ? 4 : 2;             // bytes per element
     constexpr int SPC = TF32 ? 2 : 1;            // 128-byte-wide slabs per 64-channel output chunk
@@ -709,6 +709,10 @@ static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weig
         st[1] = st[0] * p->out_dims[2];
         st[2] = st[1] * p->out_dims[1];
         st[3] = st[2] * p->out_dims[0];
+        if (y_strides != nullptr) {   // y is a strided view: element strides along X, Y, Z and between scenes
+            st[0] = (cuuint64_t)y_strides[2] * ES, st[1] = (cuuint64_t)y_strides[1] * ES;
+            st[2] = (cuuint64_t)y_strides[0] * ES, st[3] = (cuuint64_t)y_strides[3] * ES;
+        }
         const cuuint32_t box[5] = {128 / ES, (cuuint32_t)(a.box[2] * a.up[2]), (cuuint32_t)(a.box[1] * a.up[1]),
                                    (cuuint32_t)(a.box[0] * a.up[0]), 1};
         const cuuint32_t es[5] = {1, (cuuint32_t)a.up[2], (cuuint32_t)a.up[1], (cuuint32_t)a.up[0], 1};
@@ -762,4 +766,20 @@ extern "C" int ivx_conv3d_ndhwc_tf32_tc(const ivx_conv3d_params *p, const float 
                  reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
                 "tensors must be 16-byte aligned");
     return launch_tc<true>(p, x, weight, scale, shift, residual, y, workspace, workspace_bytes, (cudaStream_t)stream);
+}
+
+extern "C" int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *p, const float *x, const float *weight,
+                                             const float *scale, const float *shift, float *y,
+                                             const int64_t *y_strides, void *workspace, int64_t workspace_bytes,
+                                             void *stream) {
+    IVX_REQUIRE(p && x && weight && y && y_strides, "NULL argument");
+    int rc0 = validate_tc(p, false, true);
+    if (rc0 != IVX_OK) return rc0;
+    IVX_REQUIRE(p->in_dtype == IVX_F32 && !p->transposed, "plain convolutions of fp32 tensors only");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(weight)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    for (int i = 0; i < 4; ++i)
+        IVX_REQUIRE(y_strides[i] > 0 && y_strides[i] % 4 == 0, "output strides must be positive multiples of 4 elements");
+    return launch_tc<true>(p, x, weight, scale, shift, nullptr, y, workspace, workspace_bytes, (cudaStream_t)stream,
+                           y_strides);
 }

@@ -280,3 +280,81 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
     IVX_CHECK_LAUNCH("conv3d wgrad (tensor cores) launch");
     return IVX_OK;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Channel-major copies for the weight-gradient kernel: x [batch][X][Y][Z][C] (channels-last) ->
+//   out [n_shifts][batch][C][D2][D1][row_pitch]     out[j][..][o] = x[..][o + shift0 + j] along axis D0
+// (zero where o + shift is outside the volume, and in the padding o >= out_len of every row).
+// 32 x 32 tiles of (position along D0, channel) go through shared memory: reads are contiguous
+// along channels, writes along D0; the shifted copies re-read the same lines from L1/L2.
+// ---------------------------------------------------------------------------------------------
+namespace ivx {
+
+struct CmArgs {
+    const float *x;
+    float *out;
+    int C, n_shifts, shift0;
+    int d0, d1, d2;                  // input extents along the permuted axes
+    long long s0, s1, s2, sb;        // element strides of those axes (and of the batch) in x
+    int out_len, row_pitch;          // valid positions and allocated length of an output row
+    int o_tiles;
+    long long lines;                 // batch * d2 * d1
+};
+
+__global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
+    __shared__ float tile[32][33];
+    const long long blk = blockIdx.x;
+    const int ot = (int)(blk % a.o_tiles);
+    const long long line = blk / a.o_tiles;
+    const int i1 = (int)(line % a.d1);
+    const long long t = line / a.d1;
+    const int i2 = (int)(t % a.d2), b = (int)(t / a.d2);
+    const int c0 = blockIdx.y * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8 threads
+    const float *src = a.x + b * a.sb + i2 * a.s2 + i1 * a.s1;
+    for (int j = 0; j < a.n_shifts; ++j) {
+        const int shift = a.shift0 + j;
+#pragma unroll
+        for (int r = ty; r < 32; r += 8) {           // rows = positions, columns = channels (coalesced reads)
+            const int o = ot * 32 + r, i = o + shift;
+            float v = 0.f;
+            if (o < a.out_len && i >= 0 && i < a.d0 && c0 + tx < a.C) v = __ldg(src + i * a.s0 + c0 + tx);
+            tile[r][tx] = v;
+        }
+        __syncthreads();
+        float *dst = a.out + ((((long long)j * (a.lines / ((long long)a.d1 * a.d2)) + b) * a.C) * a.d2 * a.d1) * a.row_pitch;
+#pragma unroll
+        for (int r = ty; r < 32; r += 8) {           // rows = channels, columns = positions (coalesced writes)
+            const int c = c0 + r, o = ot * 32 + tx;
+            if (c < a.C && o < a.row_pitch)
+                dst[(((long long)c * a.d2 + i2) * a.d1 + i1) * a.row_pitch + o] = tile[tx][r];
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace ivx
+
+extern "C" int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int32_t *dims, int32_t n_channels,
+                                       const int32_t *axes, int32_t n_shifts, int32_t shift0, int32_t out_len,
+                                       int32_t row_pitch, float *out, void *stream) {
+    IVX_REQUIRE(x && dims && axes && out, "NULL argument");
+    IVX_REQUIRE(batch > 0 && n_channels > 0 && n_shifts > 0 && out_len > 0 && row_pitch >= out_len,
+                "bad sizes");
+    for (int i = 0; i < 3; ++i) IVX_REQUIRE(dims[i] > 0 && axes[i] >= 0 && axes[i] < 3, "bad dims / axes");
+    IVX_REQUIRE(axes[0] != axes[1] && axes[0] != axes[2] && axes[1] != axes[2], "axes must be a permutation");
+    const long long st[3] = {(long long)dims[1] * dims[2] * n_channels, (long long)dims[2] * n_channels, n_channels};
+    ivx::CmArgs a;
+    a.x = x, a.out = out, a.C = n_channels, a.n_shifts = n_shifts, a.shift0 = shift0;
+    a.d0 = dims[axes[0]], a.d1 = dims[axes[1]], a.d2 = dims[axes[2]];
+    a.s0 = st[axes[0]], a.s1 = st[axes[1]], a.s2 = st[axes[2]], a.sb = st[0] * dims[0];
+    a.out_len = out_len, a.row_pitch = row_pitch;
+    a.o_tiles = (row_pitch + 31) / 32;
+    a.lines = (long long)batch * a.d2 * a.d1;
+    const long long blocks = a.lines * a.o_tiles;
+    IVX_REQUIRE(blocks < (1ll << 31), "too many voxels");
+    dim3 grid((unsigned)blocks, (unsigned)((n_channels + 31) / 32));
+    ivx::channel_major_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    IVX_CHECK_LAUNCH("channel-major copy launch");
+    return IVX_OK;
+}

@@ -69,28 +69,19 @@ def _conv_tf32(fc, params, x, w_tc, bias, y):
 
 
 def _channel_major(t, axes, shifts=None, out_len=None):
-    """[B, X, Y, Z, C] -> dense [B, C, D2, D1, D0p] with D_i = axis axes[i], rows padded to 4 elements, and
-    the element pitches of dimensions 1..4 (what ivx_conv3d_wgrad_tf32_tc takes).  With ``shifts`` the
-    result is [len(shifts), B, C, D2, D1, Lp]: copy j holds ``t[.., o + shifts[j]]`` at ``o < out_len``
-    (zero outside the volume)."""
-    v = t.permute(0, 4, 1 + axes[2], 1 + axes[1], 1 + axes[0])
-    d0 = v.shape[-1]
-    if shifts is None:
-        d0p = -(-d0 // 4) * 4
-        if d0p == d0:
-            out = v.contiguous()
-        else:
-            out = torch.zeros(tuple(v.shape[:-1]) + (d0p,), dtype=t.dtype, device=t.device)
-            out[..., :d0].copy_(v)
-    else:
-        d0p = -(-out_len // 4) * 4
-        out = torch.zeros((len(shifts),) + tuple(v.shape[:-1]) + (d0p,), dtype=t.dtype, device=t.device)
-        for j, s in enumerate(shifts):
-            lo, hi = max(0, -s), min(out_len, d0 - s)
-            if hi > lo:
-                out[j, ..., lo:hi].copy_(v[..., lo + s:hi + s])
-    c, d2, d1 = out.shape[-4], out.shape[-3], out.shape[-2]
-    return out, _lib.i64([d0p, d0p * d1, d0p * d1 * d2, c * d0p * d1 * d2])
+    """[B, X, Y, Z, C] -> dense [n, B, C, D2, D1, Lp] with D_i = axis axes[i], rows padded to 4 elements, and
+    the element pitches of dimensions 1..4 (what ivx_conv3d_wgrad_tf32_tc takes).  Copy j holds
+    ``t[.., o + shifts[j]]`` at ``o < out_len`` (zero outside the volume); default: one unshifted copy."""
+    assert t.is_contiguous() and t.dtype == torch.float32
+    b, dims, c = t.shape[0], tuple(t.shape[1:4]), t.shape[4]
+    shifts = shifts or [0]
+    out_len = out_len or dims[axes[0]]
+    pitch = -(-out_len // 4) * 4
+    d1, d2 = dims[axes[1]], dims[axes[2]]
+    out = torch.empty((len(shifts), b, c, d2, d1, pitch), dtype=torch.float32, device=t.device)
+    _call("ivx_channel_major_ndhwc", t.data_ptr(), b, _lib.i32(dims), c, _lib.i32(axes), len(shifts), shifts[0],
+          out_len, pitch, out.data_ptr())
+    return out, _lib.i64([pitch, pitch * d1, pitch * d1 * d2, c * pitch * d1 * d2])
 
 
 def _wgrad_tf32(p, x, dz):
@@ -103,13 +94,78 @@ def _wgrad_tf32(p, x, dz):
         return None
     axes = list(axes)
     a0 = axes[0]        # innermost axis: its tap shift is baked into one copy of x per tap position
+    if PROFILE is not None:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
     x_t, x_pitch = _channel_major(x, axes, shifts=[j - p.pad[a0] for j in range(p.kernel[a0])],
                                   out_len=p.out_dims[a0])
     dz_t, dz_pitch = _channel_major(dz, axes)
+    if PROFILE is not None:
+        e1.record()
+        torch.cuda.synchronize()
+        rec = PROFILE.setdefault("(both channel-major copies of a layer)", [0, 0.0])
+        rec[0] += 1
+        rec[1] += e0.elapsed_time(e1)
     k = tuple(p.kernel)
     dw = torch.zeros((k[0], k[1], k[2], p.c_out, p.c_in), dtype=torch.float32, device=x.device)
     _call("ivx_conv3d_wgrad_tf32_tc", p, x_t.data_ptr(), x_pitch, dz_t.data_ptr(), dz_pitch, dw.data_ptr())
     return dw.permute(3, 4, 0, 1, 2)        # torch's [Cout, Cin, kX, kY, kZ]
+
+
+def _dgrad_strided_tf32(fc, p, dz, wp, dx):
+    """Data gradient of a strided convolution on the tensor cores, phase by phase.
+
+    Input voxels i = s*j + r (phase r, per axis) only receive the taps t with (r + pad - t) % s == 0, from the
+    outputs o = j + (r + pad - t) / s: a stride-1 convolution of ``dz`` with that subset of the kernel,
+    written into the strided view dx[r::s].  ``wp`` is the layer's weight as [kX][kY][kZ][Cin][Cout]."""
+    s3, k3, p3 = list(p.stride), list(p.kernel), list(p.pad)
+    in_dims, out_dims = tuple(p.in_dims), tuple(p.out_dims)
+    cin, cout = p.c_in, p.c_out
+    # per axis and phase: the taps (in the order of increasing o - j) and the low-side padding
+    plans = []
+    for d in range(3):
+        per_phase = []
+        for r in range(s3[d]):
+            taps = [t for t in range(k3[d]) if (r + p3[d] - t) % s3[d] == 0]
+            if not taps:
+                per_phase.append(None)
+                continue
+            e = {t: (r + p3[d] - t) // s3[d] for t in taps}
+            e_min, e_max = min(e.values()), max(e.values())
+            by_u = {e[t] - e_min: t for t in taps}
+            per_phase.append(([by_u.get(u) for u in range(e_max - e_min + 1)], -e_min))
+        plans.append(per_phase)
+    if any(ph is not None and ph[1] < 0 for per in plans for ph in per):
+        return False
+    sx, sy, sz = in_dims[1] * in_dims[2] * cin, in_dims[2] * cin, cin      # element strides of dx [B,X,Y,Z,Cin]
+    sb = in_dims[0] * sx
+    full = all(ph is not None for per in plans for ph in per)
+    if not full:
+        dx.zero_()                  # phases no tap reaches keep a zero gradient
+    for r0, ph0 in enumerate(plans[0]):
+        for r1, ph1 in enumerate(plans[1]):
+            for r2, ph2 in enumerate(plans[2]):
+                if ph0 is None or ph1 is None or ph2 is None:
+                    continue
+                view_dims = tuple(-(-(in_dims[d] - r) // s3[d]) for d, r in enumerate((r0, r1, r2)))
+                if min(view_dims) <= 0:
+                    continue
+                sel = [ph0[0], ph1[0], ph2[0]]
+                w = wp.new_zeros((cin, len(sel[0]), len(sel[1]), len(sel[2]), cout))
+                for u0, t0 in enumerate(sel[0]):
+                    for u1, t1 in enumerate(sel[1]):
+                        for u2, t2 in enumerate(sel[2]):
+                            if t0 is not None and t1 is not None and t2 is not None:
+                                w[:, u0, u1, u2, :] = wp[t0, t1, t2]
+                q = _copy_params(p, c_in=cout, c_out=cin, in_dims=out_dims, out_dims=view_dims,
+                                 kernel=tuple(len(x) for x in sel), stride=(1, 1, 1), pad=(ph0[1], ph1[1], ph2[1]),
+                                 relu=0, residual_after_act=0, post_scale=1.0)
+                ws = fc._workspace(q, dz.device)
+                base = dx.data_ptr() + 4 * (r0 * sx + r1 * sy + r2 * sz)
+                _call("ivx_conv3d_ndhwc_tf32_tc_view", q, dz.data_ptr(), w.data_ptr(), None, None, base,
+                      _lib.i64([s3[0] * sx, s3[1] * sy, s3[2] * sz, sb]),
+                      ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
+    return True
 
 
 def _copy_params(p, **changes):
@@ -241,6 +297,8 @@ class _FusedLayer(torch.autograd.Function):
                                  residual_after_act=0, post_scale=1.0)
                 w_flip = wp.flip(0, 1, 2).permute(3, 0, 1, 2, 4).contiguous()   # [k][k][k][Cin][Cout] -> [Cin][k'][Cout]
                 _conv_tf32(fc, q, dz, w_flip, None, dx)
+            elif _tf32_ok(cout, cin) and _dgrad_strided_tf32(fc, p, dz, wp, dx):
+                pass                                               # strided layer: one tensor-core launch per phase
             else:
                 wt = wp.permute(0, 1, 2, 4, 3).contiguous()        # [taps][Cin][Cout] -> [taps][Cout][Cin]
                 _call("ivx_conv3d_dgrad_ndhwc", p, dz.data_ptr(), wt.data_ptr(), dx.data_ptr())

@@ -432,6 +432,19 @@ IVX_API int ivx_conv3d_wgrad_ndhwc(const ivx_conv3d_params *params, const float 
                                    float *grad_w, void *stream);
 
 /*
+ * ivx_conv3d_ndhwc_tf32_tc_view -- ivx_conv3d_ndhwc_tf32_tc writing into a strided VIEW of a larger
+ * channels-last tensor: y_strides (host[4]) are the element strides of y along X, Y, Z and between
+ * scenes (channels stay contiguous), out_dims the extent of the view.  out_dims need not follow from
+ * in_dims (reads beyond x are zeros).  No residual.  The data gradient of a strided convolution is
+ * computed with it, one call per input phase: the inputs i = s*j + r of phase r receive a stride-1
+ * convolution of grad_z with the taps that reach them, stored at y = grad_x + r with strides s.
+ */
+IVX_API int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *params, const float *x, const float *weight,
+                                          const float *scale, const float *shift, float *y,
+                                          const int64_t *y_strides /* host[4] */, void *workspace,
+                                          int64_t workspace_bytes, void *stream);
+
+/*
  * ivx_conv3d_wgrad_tf32_tc -- the weight gradient on the tensor cores (tf32 math), for plain
  * convolutions with c_in, c_out multiples of 32 and stride 1 along at least one axis:
  *   grad_w[tap][c_out][c_in] += sum_o grad_z[o][c_out] * x[o * stride - pad + tap][c_in]
@@ -448,6 +461,17 @@ IVX_API int ivx_conv3d_wgrad_ndhwc(const ivx_conv3d_params *params, const float 
  * the copies of x_t follow each other at batch * x_pitch[3].
  * IVX_ERR_UNSUPPORTED for other layers (callers use ivx_conv3d_wgrad_ndhwc).
  */
+/*
+ * ivx_channel_major_ndhwc -- the operand copies ivx_conv3d_wgrad_tf32_tc takes, from a channels-last
+ * tensor x [batch][X][Y][Z][C] (dims = {X, Y, Z}):
+ *   out [n_shifts][batch][C][D2][D1][row_pitch],  out[j][..][o] = x[..][o + shift0 + j] along axis D0
+ * with D_i = axis axes[i]; zero where o + shift falls outside the volume and for o >= out_len.
+ * grad_z: n_shifts = 1, shift0 = 0, out_len = its extent along D0.  x: n_shifts = kernel[axes[0]],
+ * shift0 = -pad[axes[0]], out_len = out_dims[axes[0]].
+ */
+IVX_API int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int32_t *dims /* host[3] */,
+                                    int32_t n_channels, const int32_t *axes /* host[3] */, int32_t n_shifts,
+                                    int32_t shift0, int32_t out_len, int32_t row_pitch, float *out, void *stream);
 IVX_API int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *params, int32_t *axes /* host[3] */);
 IVX_API int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *params, const float *x_t,
                                      const int64_t *x_pitch /* host[4] */, const float *dz_t,
