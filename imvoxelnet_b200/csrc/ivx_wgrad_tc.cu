@@ -5,12 +5,12 @@
 // is, per tap, a GEMM whose reduction runs over VOXELS.  tcgen05 wants both operands K-major in
 // shared memory, i.e. voxels contiguous: the caller hands in channel-major ("transposed") copies
 //   dz_t [batch][c_out][D2][D1][D0]     x_t [batch][c_in][I2][I1][I0]      (fp32, D0 fastest)
-// where (D0, D1, D2) is a permutation of the layer's (X, Y, Z) chosen so that the innermost axis has
-// stride 1 (the TMA cannot stride its innermost dimension); rows may be padded (pitches are given).
+// where (D0, D1, D2) is a permutation of the layer's (X, Y, Z); rows may be padded (pitches are given).
 // The TMA also wants the innermost coordinate of a swizzled box 16-byte aligned (measured: an x box
 // starting one voxel to the left is an illegal instruction), so the tap shift along the innermost axis
-// cannot be a coordinate: x_t holds one copy per tap position along that axis, already shifted,
-//   x_t [k0][batch][c_in][I2][I1][D0]     x_t[j][..][o] = x[..][o - pad0 + j]   (0 outside)
+// cannot be a coordinate (nor can its innermost dimension be strided): x_t holds one copy per tap
+// position along that axis, already shifted and sub-sampled by the layer stride,
+//   x_t [k0][batch][c_in][I2][I1][D0]     x_t[j][..][o] = x[..][o * stride0 - pad0 + j]   (0 outside)
 // and tap t0 reads copy t0 at the output coordinate itself.
 // A k-step is a run of 32 output voxels along D0: one 5-D TMA box load per operand puts
 // [channel rows][32 voxels] = [rows][128 bytes] tiles into shared memory, 128B-swizzled -- the same
@@ -163,13 +163,12 @@ using namespace ivx;
 // Plan shared by the entry point and the layout query: which axis goes innermost.  A k-step is a run
 // of 32 voxels along that axis (one full 128-byte swizzle row per channel: boxes with a shorter inner
 // dimension are refused by the TMA in this mode -- measured -- so a short axis is padded by the
-// zero fill instead).  Candidates are the stride-1 axes; the one wasting the fewest voxels wins,
-// ties go to the tensor's own fastest axis (Z).
+// zero fill instead).  The axis wasting the fewest voxels wins, ties go to the tensor's own fastest
+// axis (Z).
 static int plan_wgrad(const ivx_conv3d_params *p, int axis[3], int box[3]) {
     int inner = -1;
     double best = -1.0;
     for (int d = 2; d >= 0; --d) {
-        if (p->stride[d] != 1) continue;
         const int n = p->out_dims[d];
         const double eff = (double)n / (double)(((n + 31) / 32) * 32);
         if (eff > best + 1e-9) best = eff, inner = d;
@@ -189,7 +188,7 @@ extern "C" int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *p, int32_t *a
         return fail(IVX_ERR_UNSUPPORTED, "tensor-core weight gradient: plain convolutions with c_in, c_out multiples of 32");
     int axis[3], box[3];
     if (plan_wgrad(p, axis, box) != 0)
-        return fail(IVX_ERR_UNSUPPORTED, "tensor-core weight gradient: at least one axis must have stride 1");
+        return fail(IVX_ERR_UNSUPPORTED, "tensor-core weight gradient: no usable axis");
     for (int i = 0; i < 3; ++i) axes[i] = axis[i];
     return IVX_OK;
 }
@@ -283,7 +282,7 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
 
 // ---------------------------------------------------------------------------------------------
 // Channel-major copies for the weight-gradient kernel: x [batch][X][Y][Z][C] (channels-last) ->
-//   out [n_shifts][batch][C][D2][D1][row_pitch]     out[j][..][o] = x[..][o + shift0 + j] along axis D0
+//   out [n_shifts][batch][C][D2][D1][row_pitch]     out[j][..][o] = x[..][o * step + shift0 + j] along axis D0
 // (zero where o + shift is outside the volume, and in the padding o >= out_len of every row).
 // 32 x 32 tiles of (position along D0, channel) go through shared memory: reads are contiguous
 // along channels, writes along D0; the shifted copies re-read the same lines from L1/L2.
@@ -293,7 +292,7 @@ namespace ivx {
 struct CmArgs {
     const float *x;
     float *out;
-    int C, n_shifts, shift0;
+    int C, n_shifts, shift0, step;
     int d0, d1, d2;                  // input extents along the permuted axes
     long long s0, s1, s2, sb;        // element strides of those axes (and of the batch) in x
     int out_len, row_pitch;          // valid positions and allocated length of an output row
@@ -316,7 +315,7 @@ __global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
         const int shift = a.shift0 + j;
 #pragma unroll
         for (int r = ty; r < 32; r += 8) {           // rows = positions, columns = channels (coalesced reads)
-            const int o = ot * 32 + r, i = o + shift;
+            const int o = ot * 32 + r, i = o * a.step + shift;
             float v = 0.f;
             if (o < a.out_len && i >= 0 && i < a.d0 && c0 + tx < a.C) v = __ldg(src + i * a.s0 + c0 + tx);
             tile[r][tx] = v;
@@ -336,16 +335,16 @@ __global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
 }  // namespace ivx
 
 extern "C" int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int32_t *dims, int32_t n_channels,
-                                       const int32_t *axes, int32_t n_shifts, int32_t shift0, int32_t out_len,
-                                       int32_t row_pitch, float *out, void *stream) {
+                                       const int32_t *axes, int32_t n_shifts, int32_t shift0, int32_t step,
+                                       int32_t out_len, int32_t row_pitch, float *out, void *stream) {
     IVX_REQUIRE(x && dims && axes && out, "NULL argument");
-    IVX_REQUIRE(batch > 0 && n_channels > 0 && n_shifts > 0 && out_len > 0 && row_pitch >= out_len,
+    IVX_REQUIRE(batch > 0 && n_channels > 0 && n_shifts > 0 && step > 0 && out_len > 0 && row_pitch >= out_len,
                 "bad sizes");
     for (int i = 0; i < 3; ++i) IVX_REQUIRE(dims[i] > 0 && axes[i] >= 0 && axes[i] < 3, "bad dims / axes");
     IVX_REQUIRE(axes[0] != axes[1] && axes[0] != axes[2] && axes[1] != axes[2], "axes must be a permutation");
     const long long st[3] = {(long long)dims[1] * dims[2] * n_channels, (long long)dims[2] * n_channels, n_channels};
     ivx::CmArgs a;
-    a.x = x, a.out = out, a.C = n_channels, a.n_shifts = n_shifts, a.shift0 = shift0;
+    a.x = x, a.out = out, a.C = n_channels, a.n_shifts = n_shifts, a.shift0 = shift0, a.step = step;
     a.d0 = dims[axes[0]], a.d1 = dims[axes[1]], a.d2 = dims[axes[2]];
     a.s0 = st[axes[0]], a.s1 = st[axes[1]], a.s2 = st[axes[2]], a.sb = st[0] * dims[0];
     a.out_len = out_len, a.row_pitch = row_pitch;

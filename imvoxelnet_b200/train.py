@@ -68,10 +68,10 @@ def _conv_tf32(fc, params, x, w_tc, bias, y):
           ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
 
 
-def _channel_major(t, axes, shifts=None, out_len=None):
+def _channel_major(t, axes, shifts=None, out_len=None, step=1):
     """[B, X, Y, Z, C] -> dense [n, B, C, D2, D1, Lp] with D_i = axis axes[i], rows padded to 4 elements, and
     the element pitches of dimensions 1..4 (what ivx_conv3d_wgrad_tf32_tc takes).  Copy j holds
-    ``t[.., o + shifts[j]]`` at ``o < out_len`` (zero outside the volume); default: one unshifted copy."""
+    ``t[.., o * step + shifts[j]]`` at ``o < out_len`` (zero outside the volume); default: one plain copy."""
     assert t.is_contiguous() and t.dtype == torch.float32
     b, dims, c = t.shape[0], tuple(t.shape[1:4]), t.shape[4]
     shifts = shifts or [0]
@@ -80,35 +80,46 @@ def _channel_major(t, axes, shifts=None, out_len=None):
     d1, d2 = dims[axes[1]], dims[axes[2]]
     out = torch.empty((len(shifts), b, c, d2, d1, pitch), dtype=torch.float32, device=t.device)
     _call("ivx_channel_major_ndhwc", t.data_ptr(), b, _lib.i32(dims), c, _lib.i32(axes), len(shifts), shifts[0],
-          out_len, pitch, out.data_ptr())
+          step, out_len, pitch, out.data_ptr())
     return out, _lib.i64([pitch, pitch * d1, pitch * d1 * d2, c * pitch * d1 * d2])
 
 
 def _wgrad_tf32(p, x, dz):
-    """Weight gradient on the tensor cores, or None when the layer is not one it takes."""
+    """Weight gradient on the tensor cores in torch's layout, or None when the layer is not one it takes."""
     from . import conv
-    if not conv._TF32 or p.transposed or p.c_in % 32 or p.c_out % 32:
+    if not conv._TF32 or p.c_in % 32 or p.c_out % 32:
         return None
+    if p.transposed:
+        # y[s*i + t] += x[i] * w[ci, co, t]: the plain convolution from the OUTPUT grid (channels c_out) to
+        # the input grid (channels c_in) with kernel == stride, whose "input" is grad_z and whose "output
+        # gradient" is x
+        q = _copy_params(p, c_in=p.c_out, c_out=p.c_in, in_dims=tuple(p.out_dims), out_dims=tuple(p.in_dims),
+                         transposed=0)
+        src, grad = dz, x
+    else:
+        q, src, grad = p, x, dz
     axes = _lib.i32([0, 0, 0])
-    if _lib.lib().ivx_conv3d_wgrad_tf32_axes(p, axes) != 0:
+    if _lib.lib().ivx_conv3d_wgrad_tf32_axes(q, axes) != 0:
         return None
     axes = list(axes)
-    a0 = axes[0]        # innermost axis: its tap shift is baked into one copy of x per tap position
+    a0 = axes[0]        # innermost axis: its tap shift and stride are baked into one copy of x per tap position
     if PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    x_t, x_pitch = _channel_major(x, axes, shifts=[j - p.pad[a0] for j in range(p.kernel[a0])],
-                                  out_len=p.out_dims[a0])
-    dz_t, dz_pitch = _channel_major(dz, axes)
+    x_t, x_pitch = _channel_major(src, axes, shifts=[j - q.pad[a0] for j in range(q.kernel[a0])],
+                                  out_len=q.out_dims[a0], step=q.stride[a0])
+    dz_t, dz_pitch = _channel_major(grad, axes)
     if PROFILE is not None:
         e1.record()
         torch.cuda.synchronize()
         rec = PROFILE.setdefault("(both channel-major copies of a layer)", [0, 0.0])
         rec[0] += 1
         rec[1] += e0.elapsed_time(e1)
-    k = tuple(p.kernel)
-    dw = torch.zeros((k[0], k[1], k[2], p.c_out, p.c_in), dtype=torch.float32, device=x.device)
-    _call("ivx_conv3d_wgrad_tf32_tc", p, x_t.data_ptr(), x_pitch, dz_t.data_ptr(), dz_pitch, dw.data_ptr())
+    k = tuple(q.kernel)
+    dw = torch.zeros((k[0], k[1], k[2], q.c_out, q.c_in), dtype=torch.float32, device=x.device)
+    _call("ivx_conv3d_wgrad_tf32_tc", q, x_t.data_ptr(), x_pitch, dz_t.data_ptr(), dz_pitch, dw.data_ptr())
+    if p.transposed:
+        return dw.permute(3, 4, 0, 1, 2)    # [k][k][k][Cin_T][Cout_T] -> torch's [Cin_T, Cout_T, kX, kY, kZ]
     return dw.permute(3, 4, 0, 1, 2)        # torch's [Cout, Cin, kX, kY, kZ]
 
 

@@ -446,17 +446,18 @@ IVX_API int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *params, const
 
 /*
  * ivx_conv3d_wgrad_tf32_tc -- the weight gradient on the tensor cores (tf32 math), for plain
- * convolutions with c_in, c_out multiples of 32 and stride 1 along at least one axis:
+ * convolutions with c_in, c_out multiples of 32 (a kernel == stride transposed layer is the plain
+ * convolution from its output grid to its input grid with the roles of x and grad_z exchanged):
  *   grad_w[tap][c_out][c_in] += sum_o grad_z[o][c_out] * x[o * stride - pad + tap][c_in]
  * (taps in kX, kY, kZ order; grad_w fp32, zero-filled by the caller; fp32 vector reductions).
  * The reduction runs over voxels, so both operands are taken CHANNEL-MAJOR:
  *   dz_t [batch][c_out][D2][D1][D0]      x_t [k0][batch][c_in][I2][I1][D0]
- * where permuted axis i is axis axes[i] of (X, Y, Z) as returned by ivx_conv3d_wgrad_tf32_axes
- * (axes[0], the innermost, always has stride 1), D = out_dims and I = in_dims in that order,
- * and k0 = kernel[axes[0]].  x_t holds one copy of x per tap position along the innermost axis,
- * already shifted:  x_t[j][..][o] = x[..][o - pad[axes[0]] + j], zero outside the volume (the TMA
- * cannot start a swizzled box at an unaligned innermost coordinate, so that shift cannot be a
- * coordinate; the shifts along the other two axes are).  x_pitch / dz_pitch: host[4], element
+ * where permuted axis i is axis axes[i] of (X, Y, Z) as returned by ivx_conv3d_wgrad_tf32_axes,
+ * D = out_dims and I = in_dims in that order, and k0 = kernel[axes[0]].  x_t holds one copy of x
+ * per tap position along the innermost axis, already shifted and sub-sampled:
+ * x_t[j][..][o] = x[..][o * stride[axes[0]] - pad[axes[0]] + j], zero outside the volume (the TMA
+ * can neither stride the innermost dimension nor start a swizzled box at an unaligned innermost
+ * coordinate, so that shift cannot be a coordinate; the shifts along the other two axes are).  x_pitch / dz_pitch: host[4], element
  * pitches of dimensions 1..4 (row, plane, channel, batch), multiples of 4 -- rows may be padded;
  * the copies of x_t follow each other at batch * x_pitch[3].
  * IVX_ERR_UNSUPPORTED for other layers (callers use ivx_conv3d_wgrad_ndhwc).
@@ -464,14 +465,16 @@ IVX_API int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *params, const
 /*
  * ivx_channel_major_ndhwc -- the operand copies ivx_conv3d_wgrad_tf32_tc takes, from a channels-last
  * tensor x [batch][X][Y][Z][C] (dims = {X, Y, Z}):
- *   out [n_shifts][batch][C][D2][D1][row_pitch],  out[j][..][o] = x[..][o + shift0 + j] along axis D0
- * with D_i = axis axes[i]; zero where o + shift falls outside the volume and for o >= out_len.
- * grad_z: n_shifts = 1, shift0 = 0, out_len = its extent along D0.  x: n_shifts = kernel[axes[0]],
- * shift0 = -pad[axes[0]], out_len = out_dims[axes[0]].
+ *   out [n_shifts][batch][C][D2][D1][row_pitch],  out[j][..][o] = x[..][o * step + shift0 + j]
+ * along axis D0, with D_i = axis axes[i]; zero where the source index falls outside the volume and
+ * for o >= out_len.  grad_z: n_shifts = 1, shift0 = 0, step = 1, out_len = its extent along D0.
+ * x: n_shifts = kernel[axes[0]], shift0 = -pad[axes[0]], step = stride[axes[0]],
+ * out_len = out_dims[axes[0]].
  */
 IVX_API int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int32_t *dims /* host[3] */,
                                     int32_t n_channels, const int32_t *axes /* host[3] */, int32_t n_shifts,
-                                    int32_t shift0, int32_t out_len, int32_t row_pitch, float *out, void *stream);
+                                    int32_t shift0, int32_t step, int32_t out_len, int32_t row_pitch,
+                                    float *out, void *stream);
 IVX_API int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *params, int32_t *axes /* host[3] */);
 IVX_API int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *params, const float *x_t,
                                      const int64_t *x_pitch /* host[4] */, const float *dz_t,
