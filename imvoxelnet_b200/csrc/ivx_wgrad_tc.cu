@@ -16,10 +16,12 @@
 // [channel rows][32 voxels] = [rows][128 bytes] tiles into shared memory, 128B-swizzled -- the same
 // K-major layout the forward kernel feeds to the MMA.  The x box starts at o * stride - pad + tap with
 // the layer stride as the TMA's element stride, so padding and ragged borders are the TMA's zero fill.
-// One CTA owns (tap, 128 output channels, up to 256 input channels, a slice of the voxel range):
-// warp 0 issues the loads, warp 1 the MMAs (M = 128 rows of c_out, N = c_in tile, K = 8 per
-// instruction, fp32 accumulator in TMEM), warps 2..5 add the accumulator into dW with 128-bit
-// vector reductions when the slice is done (dW must be zero-filled by the caller).
+// One CTA owns (a group of taps, 128 output channels, up to 256 input channels, a slice of the voxel
+// range): warp 0 issues the loads, warp 1 the MMAs (M = 128 rows of c_out, N = c_in tile, K = 8 per
+// instruction, one fp32 accumulator per tap in TMEM), warps 2..5 add the accumulators into dW with
+// 128-bit vector reductions when the slice is done (dW must be zero-filled by the caller).
+// The kernel is bound by the L2 -> shared-memory traffic (every tap re-reads both operands), so the
+// taps along axis D1 share one grad_z tile per k-step when their accumulators fit the 512 TMEM columns.
 #include "ivx_tc_ptx.cuh"
 
 namespace ivx {
@@ -39,6 +41,7 @@ struct WgArgs {
     long long steps_per_split;
     int stages;
     int a_rows;                      // rows of the grad_z box: min(c_out, 128)
+    int group;                       // taps along D1 handled by one CTA (kernel[1], or 1)
     int debug;                       // IVX_WG_DEBUG bits: 1 no TMA loads, 2 no MMAs, 4 no epilogue reads
     float *dw;                       // [taps (kx,ky,kz order)][c_out][c_in]
     TileDiv div_split, div_ci, div_co, div_c0, div_c1, div_c2;
@@ -50,13 +53,14 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int b_bytes = a.n_tile * 128;
-    const int stage_bytes = WG_A_BYTES + b_bytes;
+    const int stage_bytes = WG_A_BYTES + a.group * b_bytes;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)a.stages * stage_bytes);
     uint64_t *full_bar = bars, *empty_bar = bars + a.stages, *acc_full = bars + 2 * a.stages;
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_full + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int tmem_cols = a.n_tile <= 32 ? 32 : (a.n_tile <= 64 ? 64 : (a.n_tile <= 128 ? 128 : 256));
+    const int acc_cols = a.n_tile * a.group;
+    const int tmem_cols = acc_cols <= 32 ? 32 : (acc_cols <= 64 ? 64 : (acc_cols <= 128 ? 128 : (acc_cols <= 256 ? 256 : 512)));
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < a.stages; ++s) {
@@ -78,8 +82,10 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
     int item = blockIdx.x, split, ci_t, co_t;
     item = a.div_split.divmod(item, split);
     item = a.div_ci.divmod(item, ci_t);
-    const int tap_p = a.div_co.divmod(item, co_t);          // tap index in permuted-axis order
-    const int t0 = tap_p % a.kernel[0], t1 = (tap_p / a.kernel[0]) % a.kernel[1], t2 = tap_p / (a.kernel[0] * a.kernel[1]);
+    const int tap_g = a.div_co.divmod(item, co_t);          // tap group: (t0, t2) and, if group == 1, t1
+    const int t0 = tap_g % a.kernel[0];
+    const int t1_lo = a.group > 1 ? 0 : (tap_g / a.kernel[0]) % a.kernel[1];
+    const int t2 = a.group > 1 ? tap_g / a.kernel[0] : tap_g / (a.kernel[0] * a.kernel[1]);
     const long long k_lo = (long long)split * a.steps_per_split;
     const long long k_hi = k_lo + a.steps_per_split < a.k_steps ? k_lo + a.steps_per_split : a.k_steps;
 
@@ -99,11 +105,14 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
                     mbar_arrive(bar);
                 } else {
                     // a box always arrives in full, whatever part of it lies outside the tensor
-                    mbar_expect_tx(bar, (uint32_t)(((a.debug & 8) ? 0 : a.a_rows * 128) + ((a.debug & 16) ? 0 : b_bytes)));
+                    mbar_expect_tx(bar, (uint32_t)(((a.debug & 8) ? 0 : a.a_rows * 128) +
+                                                   ((a.debug & 16) ? 0 : a.group * b_bytes)));
                     if (!(a.debug & 8)) tma_load_5d(sa, &map_dz, bar, o0, o1, o2, co_t * 128, b);
                     if (!(a.debug & 16))
-                        tma_load_5d(sa + WG_A_BYTES, &map_x, bar, o0, o1 * a.stride[1] - a.pad[1] + t1,
-                                    o2 * a.stride[2] - a.pad[2] + t2, ci_t * a.n_tile, t0 * a.batch + b);
+                        for (int g = 0; g < a.group; ++g)
+                            tma_load_5d(sa + WG_A_BYTES + g * b_bytes, &map_x, bar, o0,
+                                        o1 * a.stride[1] - a.pad[1] + t1_lo + g, o2 * a.stride[2] - a.pad[2] + t2,
+                                        ci_t * a.n_tile, t0 * a.batch + b);
                 }
                 if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
             }
@@ -116,10 +125,14 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
                 mbar_wait(smem_u32(full_bar + stage), phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
-                const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + WG_A_BYTES);
+                const uint64_t da = umma_desc_sw128(sa);
+                for (int g = 0; g < a.group; ++g) {
+                    const uint64_t db = umma_desc_sw128(sa + WG_A_BYTES + g * b_bytes);
 #pragma unroll
-                for (int k = 0; k < 4; ++k)   // 8 voxels (32 bytes) per MMA inside the 128-byte row
-                    if (!(a.debug & 2)) umma_tf32(tmem_base, da + 2 * k, db + 2 * k, idesc, (ks > k_lo) || k != 0);
+                    for (int k = 0; k < 4; ++k)   // 8 voxels (32 bytes) per MMA inside the 128-byte row
+                        if (!(a.debug & 2))
+                            umma_tf32(tmem_base + g * a.n_tile, da + 2 * k, db + 2 * k, idesc, (ks > k_lo) || k != 0);
+                }
                 umma_commit(smem_u32(empty_bar + stage));
                 if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
             }
@@ -129,24 +142,26 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
         // epilogue: lane = output channel of the tile, columns = input channels
         const int q = warp & 3;
         const int co = co_t * 128 + q * 32 + lane;
-        // tap index in the (kx, ky, kz) order of the weight tensor
-        int k3[3];
-        k3[a.orig_axis[0]] = t0, k3[a.orig_axis[1]] = t1, k3[a.orig_axis[2]] = t2;
-        const int tap = (k3[0] * a.orig_kernel[1] + k3[1]) * a.orig_kernel[2] + k3[2];
-        float *dst = a.dw + ((long long)tap * a.c_out + co) * a.c_in + ci_t * a.n_tile;
         mbar_wait(smem_u32(acc_full), 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        for (int c = 0; c < ((a.debug & 4) ? 0 : a.n_tile); c += 32) {
-            uint32_t v[32];
-            tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + c, v);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-            if (co < a.c_out) {
+        for (int g = 0; g < a.group; ++g) {
+            // tap index in the (kx, ky, kz) order of the weight tensor
+            int k3[3];
+            k3[a.orig_axis[0]] = t0, k3[a.orig_axis[1]] = t1_lo + g, k3[a.orig_axis[2]] = t2;
+            const int tap = (k3[0] * a.orig_kernel[1] + k3[1]) * a.orig_kernel[2] + k3[2];
+            float *dst = a.dw + ((long long)tap * a.c_out + co) * a.c_in + ci_t * a.n_tile;
+            for (int c = 0; c < ((a.debug & 4) ? 0 : a.n_tile); c += 32) {
+                uint32_t v[32];
+                tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + g * a.n_tile + c, v);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (co < a.c_out) {
 #pragma unroll
-                for (int j = 0; j < 32; j += 4)
-                    if (c + j < a.n_tile)
-                        atomicAdd(reinterpret_cast<float4 *>(dst + c + j),
-                                  make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
-                                              __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+                    for (int j = 0; j < 32; j += 4)
+                        if (c + j < a.n_tile)
+                            atomicAdd(reinterpret_cast<float4 *>(dst + c + j),
+                                      make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                  __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+                }
             }
         }
     }
@@ -210,6 +225,13 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
     plan_wgrad(p, axis, a.box);
     a.c_in = p->c_in, a.c_out = p->c_out;
     a.n_tile = p->c_in % 256 == 0 ? 256 : (p->c_in % 128 == 0 ? 128 : (p->c_in % 64 == 0 ? 64 : 32));
+    // taps along D1 share the grad_z tile when their accumulators fit TMEM (<= 128 input channels each)
+    const int k1 = p->kernel[axis[1]];
+    a.group = 1;
+    if (k1 > 1 && k1 <= 4) {
+        if (a.n_tile > 128) a.n_tile = 128;
+        a.group = k1;
+    }
     a.ci_tiles = p->c_in / a.n_tile;
     a.co_tiles = (p->c_out + 127) / 128;
     a.batch = p->batch;
@@ -223,7 +245,7 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
     IVX_REQUIRE(k_steps < (1ll << 31), "too many voxels");
     a.k_steps = k_steps;
     const int n_taps = p->kernel[0] * p->kernel[1] * p->kernel[2];
-    const long long tiles = (long long)n_taps * a.co_tiles * a.ci_tiles;
+    const long long tiles = (long long)(n_taps / a.group) * a.co_tiles * a.ci_tiles;
     // enough k-slices to fill the GPU a few times over, at least 64 k-steps each
     long long splits = (4ll * kNumSMs + tiles - 1) / tiles;
     if (splits > k_steps / 64) splits = k_steps / 64;
@@ -239,7 +261,7 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
     }
     a.div_split = make_tilediv(a.k_splits), a.div_ci = make_tilediv(a.ci_tiles), a.div_co = make_tilediv(a.co_tiles);
     a.div_c0 = make_tilediv(a.chunks[0]), a.div_c1 = make_tilediv(a.chunks[1]), a.div_c2 = make_tilediv(a.chunks[2]);
-    const int stage_bytes = WG_A_BYTES + a.n_tile * 128;
+    const int stage_bytes = WG_A_BYTES + a.group * a.n_tile * 128;
     a.stages = (227 * 1024 - 2048) / stage_bytes;
     if (a.stages > 8) a.stages = 8;
     const size_t smem = (size_t)a.stages * stage_bytes + 2048;
