@@ -44,7 +44,7 @@ struct WgArgs {
     int group;                       // taps along D1 handled by one CTA (kernel[1], or 1)
     int debug;                       // IVX_WG_DEBUG bits: 1 no TMA loads, 2 no MMAs, 4 no epilogue reads
     float *dw;                       // [taps (kx,ky,kz order)][c_out][c_in]
-    TileDiv div_split, div_ci, div_co, div_c0, div_c1, div_c2;
+    TileDiv div_tap, div_ci, div_co, div_c0, div_c1, div_c2;
 };
 
 __global__ void __launch_bounds__(WG_THREADS, 1)
@@ -78,11 +78,12 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
 
-    // work item of this CTA: (k-slice, c_in tile, c_out tile, tap)
-    int item = blockIdx.x, split, ci_t, co_t;
-    item = a.div_split.divmod(item, split);
+    // work item of this CTA: (tap group, c_in tile, c_out tile, k-slice), tap group fastest: the CTAs that
+    // run at the same time work on the same voxels, so all but the first find grad_z and x in L2
+    int item = blockIdx.x, tap_g, ci_t, co_t;               // tap group: (t0, t2) and, if group == 1, t1
+    item = a.div_tap.divmod(item, tap_g);
     item = a.div_ci.divmod(item, ci_t);
-    const int tap_g = a.div_co.divmod(item, co_t);          // tap group: (t0, t2) and, if group == 1, t1
+    const int split = a.div_co.divmod(item, co_t);
     const int t0 = tap_g % a.kernel[0];
     const int t1_lo = a.group > 1 ? 0 : (tap_g / a.kernel[0]) % a.kernel[1];
     const int t2 = a.group > 1 ? tap_g / a.kernel[0] : tap_g / (a.kernel[0] * a.kernel[1]);
@@ -119,14 +120,18 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc_tf32(a.n_tile);
+            // the x tiles of a tap group lie one after the other in the stage: while they fit N <= 256 they
+            // are ONE B operand (rows = tap x input channel), i.e. a third of the MMA instructions
+            const bool fused = a.group * a.n_tile <= 256;
+            const int n_mma = fused ? a.group * a.n_tile : a.n_tile, n_groups = fused ? 1 : a.group;
+            const uint32_t idesc = umma_idesc_tf32(n_mma);
             uint32_t stage = 0, phase = 0;
             for (long long ks = k_lo; ks < k_hi; ++ks) {
                 mbar_wait(smem_u32(full_bar + stage), phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
                 const uint64_t da = umma_desc_sw128(sa);
-                for (int g = 0; g < a.group; ++g) {
+                for (int g = 0; g < n_groups; ++g) {
                     const uint64_t db = umma_desc_sw128(sa + WG_A_BYTES + g * b_bytes);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)   // 8 voxels (32 bytes) per MMA inside the 128-byte row
@@ -259,7 +264,7 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
         const char *e = getenv("IVX_WG_DEBUG");
         a.debug = e ? atoi(e) : 0;
     }
-    a.div_split = make_tilediv(a.k_splits), a.div_ci = make_tilediv(a.ci_tiles), a.div_co = make_tilediv(a.co_tiles);
+    a.div_tap = make_tilediv(n_taps / a.group), a.div_ci = make_tilediv(a.ci_tiles), a.div_co = make_tilediv(a.co_tiles);
     a.div_c0 = make_tilediv(a.chunks[0]), a.div_c1 = make_tilediv(a.chunks[1]), a.div_c2 = make_tilediv(a.chunks[2]);
     const int stage_bytes = WG_A_BYTES + a.group * a.n_tile * 128;
     a.stages = (227 * 1024 - 2048) / stage_bytes;
