@@ -432,6 +432,14 @@ def run_ours(args):
                         "kernel": "conv3d_tc_halo_kernel / conv3d_tc_kernel", "peak_kind": peak_kind + " (sustained)",
                         "algorithmic_flops_per_step": neck_gflop * batch * 1e9,
                         "launches_per_step": launches // max(args.steps, 1) - 1}
+        elif args.neck_precision == "tf32":
+            # same kernel with kind::tf32 MMAs; no measured tf32 peak in MEASURED_PEAKS.json: half the
+            # bf16 figure is the nominal ratio of the two tensor rates (1.1 vs 2.25 PFLOP/s dense)
+            roofline = {"bound": "tensor", "achieved": tflops, "peak": peak / 2, "unit": "TFLOP/s",
+                        "frac": tflops / (peak / 2), "traffic": None, "kernel": "conv3d_tc_kernel<tf32>",
+                        "peak_kind": peak_kind + " (sustained bf16) / 2: nominal tf32 : bf16 ratio",
+                        "algorithmic_flops_per_step": neck_gflop * batch * 1e9,
+                        "launches_per_step": launches // max(args.steps, 1) - 1}
 
     # ---- end to end: host buffers in, host buffers out, every step ----
     with torch.no_grad():
@@ -551,8 +559,9 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="kitti", choices=sorted(WORKLOADS))
-    ap.add_argument("--neck-precision", default="bf16", choices=["bf16", "fp32"],
-                    help="bf16: tcgen05 kernels (1e-2 of the reference); fp32: CUDA-core parity path (1e-5)")
+    ap.add_argument("--neck-precision", default="bf16", choices=["bf16", "tf32", "fp32"],
+                    help="bf16: tcgen05 kernels (1e-2 of the reference); tf32: fp32 tensors, tf32 tensor-core math "
+                         "(5e-3); fp32: CUDA-core parity path (1e-5)")
     ap.add_argument("--no-neck", action="store_true", help="time the back-projection stage only")
     ap.add_argument("--feature-dtype", default="f32", choices=["f32", "bf16"],
                     help="dtype of the 2D feature maps (the reference's are fp32; bf16 halves the gather)")

@@ -61,7 +61,7 @@ def test_every_reference_config_builds():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("precision", ["fp32", "bf16"])
+@pytest.mark.parametrize("precision", ["fp32", "tf32", "bf16"])
 def test_extract_feat_matches_the_reference_loop(precision):
     from oracle import torch_necks, torch_port
     from imvoxelnet_b200 import projection as pj
@@ -103,27 +103,30 @@ def test_extract_feat_matches_the_reference_loop(precision):
         want = ref_neck(torch.stack(vols))
         want_valid = torch.stack(vals)
     assert feats2d is None and torch.equal(valids, want_valid)
-    rel = 1e-5 if precision == "fp32" else 1e-2
+    rel = {"fp32": 1e-5, "tf32": 5e-3, "bf16": 1e-2}[precision]
     for a, b in zip(outs, want):
         assert a.shape == b.shape
         assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=rel, atol=1e-6 if precision == "fp32" else 1e-3)
 
 
 @pytest.mark.gpu
-def test_extract_feat_is_differentiable_in_training_mode():
+@pytest.mark.parametrize("precision,channels", [("fp32", 16), ("tf32", 64)])
+def test_extract_feat_is_differentiable_in_training_mode(precision, channels):
     """images -> 2D net -> fused back-projection -> neck, all under autograd: the loss
-    gradient reaches the 2D backbone and the neck parameters (forward_train, :82-87)."""
+    gradient reaches the 2D backbone and the neck parameters (forward_train, :82-87); in tf32 the
+    neck's convolutions and their gradients run on the tensor cores."""
     dev = "cuda:0"
     torch.manual_seed(0)
     sc = scenes.scannet(n_views=2, seed=2)
     sc.img_meta['img_shape'] = (96, 128, 3)
     sc.img_meta['ori_shape'] = (480, 640, 3)
-    m = _build(dict(KITTI_MODEL, neck=dict(type='FPN', in_channels=[256, 512, 1024, 2048], out_channels=16,
+    m = _build(dict(KITTI_MODEL, neck=dict(type='FPN', in_channels=[256, 512, 1024, 2048], out_channels=channels,
                                            num_outs=4),
-                    neck_3d=dict(type='FastIndoorImVoxelNeck', in_channels=16, n_blocks=[1, 1, 1],
-                                 out_channels=8),
+                    neck_3d=dict(type='FastIndoorImVoxelNeck', in_channels=channels, n_blocks=[1, 1, 1],
+                                 out_channels=channels // 2 if channels < 64 else 64),
                     n_voxels=(8, 8, 8), voxel_size=(.6, .6, .4)))
     m = m.train().to(dev)
+    m.set_precision(precision)
     img = torch.randn(2, 2, 3, 96, 128, device=dev)
     outs, valids, _ = m.extract_feat(img, [sc.img_meta, sc.img_meta], 'train')
     assert valids.any()
