@@ -94,7 +94,12 @@ __device__ __forceinline__ bool project_rn(const float *P, float px, float py, f
     xr = yr = 0.f;
     if (!(p2 > 0.0f)) return false;
     const float p0 = dot4_rn(P, px, py, pz);
+    // a pixel column far outside the image needs no division: x = p0 / p2 rounds to a column in [0, w)
+    // only if -0.5 <= x < w - 0.5 (up to one rounding of the quotient, 1e-7 relative); the margins
+    // below (0.01 pixel) keep the test strictly conservative, so the result is unchanged bit for bit
+    if (p0 < -0.51f * p2 || p0 > ((float)w - 0.49f) * p2) return false;
     const float p1 = dot4_rn(P + 4, px, py, pz);
+    if (p1 < -0.51f * p2 || p1 > ((float)h - 0.49f) * p2) return false;
     xr = rintf(__fdiv_rn(p0, p2));
     yr = rintf(__fdiv_rn(p1, p2));
     // -0.0f >= 0 holds (pixel 0); NaN / inf compare false, like the reference's
