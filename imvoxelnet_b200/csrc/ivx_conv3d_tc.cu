@@ -536,7 +536,6 @@ static int validate_tc(const ivx_conv3d_params *p, bool has_residual, bool free_
 
 // does the halo-reuse kernel take this layer?  (IVX_TC_HALO=0 keeps everything on the per-tap one)
 static bool use_halo(const ivx_conv3d_params *p, int perm[3], int *mt) {
-    if (p->in_dtype != IVX_BF16) return false;   // the halo kernel is bf16 only
     static const bool halo_on = [] {
         const char *e = getenv("IVX_TC_HALO");
         return e == nullptr || e[0] != '0';
@@ -765,6 +764,11 @@ extern "C" int ivx_conv3d_ndhwc_tf32_tc(const ivx_conv3d_params *p, const float 
     IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(weight) |
                  reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
                 "tensors must be 16-byte aligned");
+    {
+        int perm[3] = {0, 1, 2}, mt = 1;
+        if (use_halo(p, perm, &mt))
+            return launch_conv3d_tc_halo(p, perm, mt, x, weight, scale, shift, residual, y, (cudaStream_t)stream);
+    }
     return launch_tc<true>(p, x, weight, scale, shift, residual, y, workspace, workspace_bytes, (cudaStream_t)stream);
 }
 

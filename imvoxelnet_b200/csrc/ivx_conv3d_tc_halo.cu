@@ -32,6 +32,12 @@
 //
 // Warp roles (224 threads): 0 activation-plane producer, 1 MMA issuer, 2 weight
 // producer, 3..6 epilogue.
+//
+// TF32 = true is the same kernel for fp32 tensors with kind::tf32 MMAs: a 128-byte row is 32 channels,
+// so a chunk is 32 input channels and the output is staged as 32-channel fp32 slabs (four per
+// 128-channel tile, which leaves room for one slab set and two plane stages).
+#include <type_traits>
+
 #include "ivx_tc_ptx.cuh"
 
 namespace ivx {
@@ -56,7 +62,7 @@ struct HaloArgs {
     int relu, residual_after_act;
     float post_scale;
     const float *scale, *shift;
-    const __nv_bfloat16 *res;
+    const void *res;
     int debug;                 // IVX_HALO_DEBUG: 1 = epilogue does no work, 2 = no MMA issued (timing decomposition only)
 };
 
@@ -77,10 +83,13 @@ __device__ __forceinline__ HaloTile decode_halo_tile(const HaloArgs &a, long lon
     return c;
 }
 
+template <bool TF32>
 __global__ void __launch_bounds__(HL_THREADS, 1)
 conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                       const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_r,
                       const __grid_constant__ HaloArgs a) {
+    constexpr int EK = TF32 ? 32 : 64;      // input channels per chunk = one 128-byte row
+    constexpr int SC = TF32 ? 32 : 64;      // output channels per 128-byte-wide slab
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t *smem = reinterpret_cast<uint8_t *>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
     const int plane_rows = HL_PPAD * (HL_QT * a.mt + 2);
@@ -117,7 +126,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
-    const int k_chunks = a.c_in / 64;
+    const int k_chunks = a.c_in / EK;
     const int n_planes = a.pack2 ? 4 : 3;          // input planes feeding one super-tile
 
     if (warp == 0) {
@@ -131,7 +140,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         mbar_wait(smem_u32(a_empty + stage), phase ^ 1);
                         const uint32_t bar = smem_u32(a_full + stage);
                         mbar_expect_tx(bar, (uint32_t)(plane_rows * 128));
-                        tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, kc * 64,
+                        tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, kc * EK,
                                     tc.p0 - a.pad[0], tc.q0 - a.pad[1], tc.r0 * a.stride_r - a.pad[2] + dr, tc.b);
                         if (++stage == (uint32_t)a.a_stages) stage = 0, phase ^= 1;
                     }
@@ -154,7 +163,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                             if (dr < 0 || dr > 2) return 27 * a.c_in;   // beyond the tensor: TMA zero fill
                             int k3[3];                                   // tap along the tensor axes X, Y, Z
                             k3[a.axis[0]] = dp, k3[a.axis[1]] = dq, k3[a.axis[2]] = dr;
-                            return ((k3[0] * 3 + k3[1]) * 3 + k3[2]) * a.c_in + kc * 64;
+                            return ((k3[0] * 3 + k3[1]) * 3 + k3[2]) * a.c_in + kc * EK;
                         };
                         if (a.pack2) {
                             mbar_expect_tx(bar, 2u * 64u * 128u);
@@ -171,7 +180,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     } else if (warp == 1) {
         // ------------------------------ MMA issuer ------------------------------
         if (lane == 0) {
-            const uint32_t idesc = umma_idesc(128 * a.mt);   // M = 128 channel lanes, N = voxels
+            const uint32_t idesc = TF32 ? umma_idesc_tf32(128 * a.mt) : umma_idesc(128 * a.mt);   // M = 128 channel lanes, N = voxels
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0, acc = 0, acc_phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
                 mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
@@ -193,8 +202,10 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                                 const uint64_t dx = umma_desc_sw128(plane + row0 * 128, HL_PPAD * 128);
                                 if (a.debug != 2) {
 #pragma unroll
-                                    for (int k = 0; k < 4; ++k)
-                                        umma_bf16(d_tmem, dw + 2 * k, dx + 2 * k, idesc, !(first && k == 0));
+                                    for (int k = 0; k < 4; ++k) {
+                                        if (TF32) umma_tf32(d_tmem, dw + 2 * k, dx + 2 * k, idesc, !(first && k == 0));
+                                        else umma_bf16(d_tmem, dw + 2 * k, dx + 2 * k, idesc, !(first && k == 0));
+                                    }
                                 }
                                 first = false;
                                 umma_commit(smem_u32(b_empty + sb));
@@ -218,11 +229,13 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
         const bool ch_ok = a.pack2 || ch_local < a.n_tile;
         const bool epi_leader = (warp == 3 && lane == 0);
         const bool has_res = a.res != nullptr;
-        // a voxel tile is stored as 64-channel slabs: the two channel halves of a 128-channel
-        // tile, or (pack2) the 64 channels of output plane r0 and of plane r0 + 1
-        const int slabs_per_tile = a.pack2 ? 2 : a.n_tile / 64;
+        // a voxel tile is stored as SC-channel slabs (128 bytes per voxel row): the channel groups of a
+        // 128-channel tile, or (pack2) those of the 64 channels of output plane r0 and then of plane r0 + 1
+        constexpr int ES = TF32 ? 4 : 2;               // bytes per output element
+        const int slabs_per_tile = a.pack2 ? 128 / SC : a.n_tile / SC;
+        const int slabs_per_plane = 64 / SC;           // pack2: slabs of one output plane
         const int slab_sets = a.n_slabs / slabs_per_tile;
-        const int my_slab = ch_local >> 6, my_chunk = (ch_local & 63) >> 3, my_byte = (ch_local & 7) * 2;
+        const int my_slab = ch_local / SC, my_chunk = ((ch_local % SC) * ES) >> 4, my_byte = ((ch_local % SC) * ES) & 15;
         uint32_t xoff[8];                              // byte offset inside a slab row, by (row & 7)
 #pragma unroll
         for (int c = 0; c < 8; ++c) xoff[c] = (uint32_t)(((my_chunk ^ c) << 4) + my_byte);
@@ -241,13 +254,13 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             mbar_expect_tx(bar, (uint32_t)(slabs_per_tile * 128 * 128));
             for (int sl = 0; sl < slabs_per_tile; ++sl)
                 tma_load_5d(smem_u32(slab_base + (size_t)(into * slabs_per_tile + sl) * (128 * 128)), &map_r, bar,
-                            tc.n0 + (a.pack2 ? 0 : sl * 64), tc.p0, tc.q0 + mt * HL_QT, tc.r0 + (a.pack2 ? sl : 0),
-                            tc.b);
+                            tc.n0 + (a.pack2 ? (sl % slabs_per_plane) * SC : sl * SC), tc.p0, tc.q0 + mt * HL_QT,
+                            tc.r0 + (a.pack2 ? sl / slabs_per_plane : 0), tc.b);
         };
 
         for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
             const HaloTile tc = decode_halo_tile(a, t);
-            const int ch = tc.n0 + (a.pack2 ? (ch_local & 63) : ch_local);
+            const int ch = tc.n0 + (a.pack2 ? (ch_local & 63) : ch_local);   // (pack2: my_slab already selects the plane)
             const float sc = (a.scale && ch_ok) ? __ldg(a.scale + ch) : 1.f;
             const float sh = (a.shift && ch_ok) ? __ldg(a.shift + ch) : 0.f;
             // residual tiles are fetched while the accumulator is still being produced: all of the
@@ -278,17 +291,18 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         uint8_t *rows = my_rows + v0 * 128;
 #pragma unroll
                         for (int j = 0; j < 32; ++j) {
-                            __nv_bfloat16 *cell = reinterpret_cast<__nv_bfloat16 *>(rows + j * 128 + xoff[j & 7]);
+                            using Cell = typename std::conditional<TF32, float, __nv_bfloat16>::type;
+                            Cell *cell = reinterpret_cast<Cell *>(rows + j * 128 + xoff[j & 7]);
                             float f = fmaf(__uint_as_float(v[j]), sc, sh);
                             if (has_res) {
-                                const float r = __bfloat162float(*cell);
+                                const float r = (float)*cell;
                                 if (!a.residual_after_act) f += r;
                                 if (a.relu) f = fmaxf(f, 0.f);
                                 if (a.residual_after_act) f += r;
                             } else if (a.relu) {
                                 f = fmaxf(f, 0.f);
                             }
-                            *cell = __float2bfloat16_rn(f * a.post_scale);
+                            *cell = (Cell)(f * a.post_scale);
                         }
                     }
                 }
@@ -297,8 +311,8 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                 if (epi_leader) {
                     for (int sl = 0; sl < slabs_per_tile; ++sl)
                         tma_store_5d(&map_y, smem_u32(slab_base + (size_t)(set * slabs_per_tile + sl) * (128 * 128)),
-                                     tc.n0 + (a.pack2 ? 0 : sl * 64), tc.p0, tc.q0 + mt * HL_QT,
-                                     tc.r0 + (a.pack2 ? sl : 0), tc.b);
+                                     tc.n0 + (a.pack2 ? (sl % slabs_per_plane) * SC : sl * SC), tc.p0,
+                                     tc.q0 + mt * HL_QT, tc.r0 + (a.pack2 ? sl / slabs_per_plane : 0), tc.b);
                     asm volatile("cp.async.bulk.commit_group;" ::: "memory");
                 }
                 if (++set == slab_sets) set = 0;
@@ -319,7 +333,8 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
 // Decide whether (and how) the halo kernel takes a layer.  perm[role] = tensor axis (0=X,1=Y,2=Z)
 // playing role P, Q, R.  Returns the fraction of accumulator rows that hold real outputs, or 0.
 double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
-    if (p->transposed || p->c_in % 64 != 0 || p->c_out % 64 != 0) return 0.0;
+    const int ek = p->in_dtype == IVX_F32 ? 32 : 64;     // channels per 128-byte row: tf32 / bf16
+    if (p->transposed || p->c_in % ek != 0 || p->c_out % 64 != 0) return 0.0;
     int strided_axis = -1;
     for (int d = 0; d < 3; ++d) {
         if (p->kernel[d] != 3 || p->pad[d] > 1) return 0.0;
@@ -355,9 +370,13 @@ double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
     return (double)p->out_dims[perm[0]] * p->out_dims[perm[1]] / (double)(tp * HL_P * tq * HL_QT * *mt_out);
 }
 
-int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
-                          const void *weight_bf16, const float *scale, const float *shift,
-                          const void *residual, void *y, cudaStream_t stream) {
+template <bool TF32>
+static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
+                       const void *weight_bf16, const float *scale, const float *shift,
+                       const void *residual, void *y, cudaStream_t stream) {
+    constexpr int EK = TF32 ? 32 : 64, SC = TF32 ? 32 : 64, ES = TF32 ? 4 : 2;
+    const CUtensorMapDataType dt_in = TF32 ? CU_TENSOR_MAP_DATA_TYPE_TFLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    const CUtensorMapDataType dt_out = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     HaloArgs a;
     a.c_in = p->c_in, a.c_out = p->c_out;
     a.n_tile = p->c_out % 128 == 0 ? 128 : 64;
@@ -383,22 +402,26 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
     a.tiles[2] = a.pack2 ? (a.dims[2] + 1) / 2 : a.dims[2];
     a.n_tiles = (long long)p->batch * a.tiles[0] * a.tiles[1] * a.tiles[2] * a.n_splits;
     a.relu = p->relu, a.residual_after_act = p->residual_after_act, a.post_scale = p->post_scale;
-    a.scale = scale, a.shift = shift, a.res = static_cast<const __nv_bfloat16 *>(residual);
+    a.scale = scale, a.shift = shift, a.res = residual;
     {
         const char *e = getenv("IVX_HALO_DEBUG");
         a.debug = e ? atoi(e) : 0;
     }
     const int plane_rows = HL_PPAD * (HL_QT * mt + 2);
     const int a_bytes = (plane_rows * 128 + 1023) & ~1023, b_bytes = 128 * 128;
-    const int slabs_per_tile = a.pack2 ? 2 : a.n_tile / 64;
+    const int slabs_per_tile = a.pack2 ? 128 / SC : a.n_tile / SC;
     // shared memory: weight ring (16 KB stages), two sets of output slabs if they fit, the
     // rest goes to activation planes (each one feeds 36 MMAs)
     a.b_stages = 4;
     a.n_slabs = 2 * slabs_per_tile;
     const int budget = 227 * 1024 - 2048;
     a.a_stages = (budget - a.b_stages * b_bytes - a.n_slabs * 16384) / a_bytes;
-    if (a.a_stages < 3 && slabs_per_tile == 2) {   // 128-channel tiles: one slab set buys a plane stage
+    if (a.a_stages < 3 && slabs_per_tile >= 2) {   // wide tiles: one slab set buys plane stages
         a.n_slabs = slabs_per_tile;
+        a.a_stages = (budget - a.b_stages * b_bytes - a.n_slabs * 16384) / a_bytes;
+    }
+    if (a.a_stages < 2) {                          // fp32 slabs are large: a shorter weight ring
+        a.b_stages = 3;
         a.a_stages = (budget - a.b_stages * b_bytes - a.n_slabs * 16384) / a_bytes;
     }
     if (a.a_stages > 4) a.a_stages = 4;
@@ -411,44 +434,52 @@ int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt,
         const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[perm[0]],
                                     (cuuint64_t)p->in_dims[perm[1]], (cuuint64_t)p->in_dims[perm[2]],
                                     (cuuint64_t)p->batch};
-        const cuuint64_t st[4] = {(cuuint64_t)in_s[perm[0]] * 2, (cuuint64_t)in_s[perm[1]] * 2,
-                                  (cuuint64_t)in_s[perm[2]] * 2, (cuuint64_t)in_s[0] * p->in_dims[0] * 2};
-        const cuuint32_t box[5] = {64, HL_PPAD, (cuuint32_t)(HL_QT * mt + 2), 1, 1};
+        const cuuint64_t st[4] = {(cuuint64_t)in_s[perm[0]] * ES, (cuuint64_t)in_s[perm[1]] * ES,
+                                  (cuuint64_t)in_s[perm[2]] * ES, (cuuint64_t)in_s[0] * p->in_dims[0] * ES};
+        const cuuint32_t box[5] = {EK, HL_PPAD, (cuuint32_t)(HL_QT * mt + 2), 1, 1};
         const cuuint32_t es[5] = {1, 1, 1, 1, 1};
-        int rc = encode_map_bf16(&map_x, 5, const_cast<void *>(x), dims, st, box, es, "activations (halo)");
+        int rc = encode_map_sw128(&map_x, dt_in, 5, const_cast<void *>(x), dims, st, box, es, "activations (halo)");
         if (rc != IVX_OK) return rc;
     }
     {
         const cuuint64_t dims[2] = {(cuuint64_t)27 * p->c_in, (cuuint64_t)p->c_out};
-        const cuuint64_t st[1] = {(cuuint64_t)27 * p->c_in * 2};
-        const cuuint32_t box[2] = {64, (cuuint32_t)a.n_tile};   // pack2: two such loads fill the 128 rows
+        const cuuint64_t st[1] = {(cuuint64_t)27 * p->c_in * ES};
+        const cuuint32_t box[2] = {EK, (cuuint32_t)a.n_tile};   // pack2: two such loads fill the 128 rows
         const cuuint32_t es[2] = {1, 1};
-        int rc = encode_map_bf16(&map_w, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights (halo)");
+        int rc = encode_map_sw128(&map_w, dt_in, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights (halo)");
         if (rc != IVX_OK) return rc;
     }
     {
         const cuuint64_t dims[5] = {(cuuint64_t)p->c_out, (cuuint64_t)a.dims[0], (cuuint64_t)a.dims[1],
                                     (cuuint64_t)a.dims[2], (cuuint64_t)p->batch};
-        const cuuint64_t st[4] = {(cuuint64_t)a.ostride[0] * 2, (cuuint64_t)a.ostride[1] * 2,
-                                  (cuuint64_t)a.ostride[2] * 2, (cuuint64_t)a.ostride_b * 2};
-        const cuuint32_t box[5] = {64, HL_P, HL_QT, 1, 1};
+        const cuuint64_t st[4] = {(cuuint64_t)a.ostride[0] * ES, (cuuint64_t)a.ostride[1] * ES,
+                                  (cuuint64_t)a.ostride[2] * ES, (cuuint64_t)a.ostride_b * ES};
+        const cuuint32_t box[5] = {SC, HL_P, HL_QT, 1, 1};
         const cuuint32_t es[5] = {1, 1, 1, 1, 1};
-        int rc = encode_map_bf16(&map_y, 5, y, dims, st, box, es, "output (halo)");
+        int rc = encode_map_sw128(&map_y, dt_out, 5, y, dims, st, box, es, "output (halo)");
         if (rc != IVX_OK) return rc;
         map_r = map_y;
         if (residual != nullptr) {
-            rc = encode_map_bf16(&map_r, 5, const_cast<void *>(residual), dims, st, box, es, "residual (halo)");
+            rc = encode_map_sw128(&map_r, dt_out, 5, const_cast<void *>(residual), dims, st, box, es, "residual (halo)");
             if (rc != IVX_OK) return rc;
         }
     }
-    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_halo_kernel<TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem),
                         "cudaFuncSetAttribute");
     if (rc != IVX_OK) return rc;
     const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
-    conv3d_tc_halo_kernel<<<grid, HL_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
+    conv3d_tc_halo_kernel<TF32><<<grid, HL_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
     IVX_CHECK_LAUNCH("conv3d_tc_halo launch");
     return IVX_OK;
+}
+
+int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
+                          const void *weight, const float *scale, const float *shift,
+                          const void *residual, void *y, cudaStream_t stream) {
+    if (p->in_dtype == IVX_F32)
+        return launch_halo<true>(p, perm, mt, x, weight, scale, shift, residual, y, stream);
+    return launch_halo<false>(p, perm, mt, x, weight, scale, shift, residual, y, stream);
 }
 
 }  // namespace ivx

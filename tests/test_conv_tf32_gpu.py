@@ -31,6 +31,18 @@ CASES = [
     (128, 64, (8, 8, 8), 1, 1, 0, 1),
     (64, 64, (20, 50, 4), 3, 1, 0, 1),
     (1024, 128, (10, 10, 4), 3, 1, 1, 2),      # split-K
+    # shapes the halo-reuse kernel takes (3x3x3, stride 1 or strided along one axis, well-filled tiles)
+    (64, 64, (16, 32, 6), 3, 1, 1, 1),
+    (64, 128, (5, 24, 32), 3, 1, 1, 2),
+    (128, 128, (40, 7, 16), 3, 1, 1, 1),
+    (128, 64, (18, 34, 3), 3, 1, (1, 1, 0), 1),
+    (32, 64, (20, 50, 4), 3, 1, 0, 1),
+    (96, 64, (12, 248, 3), 3, 1, 1, 1),
+    (64, 128, (16, 32, 12), 3, (1, 1, 2), 1, 1),
+    (128, 256, (8, 32, 6), 3, (1, 1, 2), 1, 2),
+    (64, 64, (13, 16, 32), 3, (2, 1, 1), 1, 1),
+    (256, 256, (16, 16, 3), 3, 1, 0, 1),
+    (128, 512, (8, 32, 4), 3, 1, 1, 1),
 ]
 
 
