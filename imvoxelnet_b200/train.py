@@ -153,6 +153,10 @@ def _dgrad_strided_tf32(fc, p, dz, wp, dx):
     full = all(ph is not None for per in plans for ph in per)
     if not full:
         dx.zero_()                  # phases no tap reaches keep a zero gradient
+    n_taps = k3[0] * k3[1] * k3[2]
+    # the layer's taps as rows, plus one zero row for the holes of a phase's sub-kernel
+    taps_ext = torch.cat((wp.reshape(n_taps, cin, cout), wp.new_zeros((1, cin, cout))))
+    cache = fc.__dict__.setdefault("_phase_index", {})
     for r0, ph0 in enumerate(plans[0]):
         for r1, ph1 in enumerate(plans[1]):
             for r2, ph2 in enumerate(plans[2]):
@@ -162,12 +166,13 @@ def _dgrad_strided_tf32(fc, p, dz, wp, dx):
                 if min(view_dims) <= 0:
                     continue
                 sel = [ph0[0], ph1[0], ph2[0]]
-                w = wp.new_zeros((cin, len(sel[0]), len(sel[1]), len(sel[2]), cout))
-                for u0, t0 in enumerate(sel[0]):
-                    for u1, t1 in enumerate(sel[1]):
-                        for u2, t2 in enumerate(sel[2]):
-                            if t0 is not None and t1 is not None and t2 is not None:
-                                w[:, u0, u1, u2, :] = wp[t0, t1, t2]
+                key = (str(dz.device), tuple(k3), tuple(s3), tuple(p3), r0, r1, r2)
+                idx = cache.get(key)
+                if idx is None:     # which tap of the layer sits at (u0, u1, u2) of this phase's sub-kernel
+                    rows = [(t0 * k3[1] + t1) * k3[2] + t2 if None not in (t0, t1, t2) else n_taps
+                            for t0 in sel[0] for t1 in sel[1] for t2 in sel[2]]
+                    idx = cache[key] = torch.tensor(rows, dtype=torch.long, device=dz.device)
+                w = taps_ext.index_select(0, idx).permute(1, 0, 2).contiguous()    # [Cin][taps'][Cout]
                 q = _copy_params(p, c_in=cout, c_out=cin, in_dims=out_dims, out_dims=view_dims,
                                  kernel=tuple(len(x) for x in sel), stride=(1, 1, 1), pad=(ph0[1], ph1[1], ph2[1]),
                                  relu=0, residual_after_act=0, post_scale=1.0)
