@@ -214,12 +214,13 @@ def test_neck_training_step_in_tf32_precision(name):
 
     # tf32 moves pre-activations by ~1e-3, which flips some ReLU masks of a deep net: isolated
     # gradient entries differ a lot, so the bar is the relative L2 error of every gradient tensor,
-    # and it is anchored on what cuDNN's tf32 does to the same gradients (ours <= 3x theirs, or 2e-2)
+    # and it is anchored on what cuDNN's tf32 does to the same gradients (ours <= 3x theirs; floor 0.1 in case
+    # cuDNN picks a non-tf32 algorithm on some box: measured 0.03-0.07 for both, a wrong kernel gives O(1))
     def rel_l2(got, want):
         return ((got - want).norm() / want.norm()).item()
 
-    assert rel_l2(xb.grad, xa.grad) <= max(3 * rel_l2(xc.grad, xa.grad), 2e-2)
+    assert rel_l2(xb.grad, xa.grad) <= max(3 * rel_l2(xc.grad, xa.grad), 1e-1)
     for (k, p), q, t in zip(ref.named_parameters(), m.parameters(), twin.parameters()):
         if p.grad is None or p.grad.abs().max().item() < 1e-3:
             continue    # conv bias in front of a batch-statistics norm: analytically zero, pure noise
-        assert rel_l2(q.grad, p.grad) <= max(3 * rel_l2(t.grad, p.grad), 2e-2), k
+        assert rel_l2(q.grad, p.grad) <= max(3 * rel_l2(t.grad, p.grad), 1e-1), k
