@@ -327,8 +327,10 @@ struct CmArgs {
     long long lines;                 // batch * d2 * d1
 };
 
+constexpr int CM_ROWS = 96;          // source positions one block stages: 31 * step + n_shifts of them
+
 __global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
-    __shared__ float tile[32][33];
+    __shared__ float tile[CM_ROWS][33];
     const long long blk = blockIdx.x;
     const int ot = (int)(blk % a.o_tiles);
     const long long line = blk / a.o_tiles;
@@ -338,24 +340,29 @@ __global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
     const int c0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8 threads
     const float *src = a.x + b * a.sb + i2 * a.s2 + i1 * a.s1;
+    const int batch = (int)(a.lines / ((long long)a.d1 * a.d2));
+    // every source position the 32 outputs of this tile need, for all shifts, read once:
+    // rows = positions, columns = channels (coalesced reads)
+    const int i_lo = ot * 32 * a.step + a.shift0;
+    const int n_rows = 31 * a.step + a.n_shifts;
+    for (int r = ty; r < n_rows; r += 8) {
+        const int i = i_lo + r;
+        float v = 0.f;
+        if (i >= 0 && i < a.d0 && c0 + tx < a.C) v = __ldg(src + i * a.s0 + c0 + tx);
+        tile[r][tx] = v;
+    }
+    __syncthreads();
+    // rows = channels, columns = output positions (coalesced writes), one pass per shifted copy
+    const int o = ot * 32 + tx;
     for (int j = 0; j < a.n_shifts; ++j) {
-        const int shift = a.shift0 + j;
+        float *dst = a.out + ((((long long)j * batch + b) * a.C) * a.d2 * a.d1) * a.row_pitch;
 #pragma unroll
-        for (int r = ty; r < 32; r += 8) {           // rows = positions, columns = channels (coalesced reads)
-            const int o = ot * 32 + r, i = o * a.step + shift;
-            float v = 0.f;
-            if (o < a.out_len && i >= 0 && i < a.d0 && c0 + tx < a.C) v = __ldg(src + i * a.s0 + c0 + tx);
-            tile[r][tx] = v;
-        }
-        __syncthreads();
-        float *dst = a.out + ((((long long)j * (a.lines / ((long long)a.d1 * a.d2)) + b) * a.C) * a.d2 * a.d1) * a.row_pitch;
-#pragma unroll
-        for (int r = ty; r < 32; r += 8) {           // rows = channels, columns = positions (coalesced writes)
-            const int c = c0 + r, o = ot * 32 + tx;
+        for (int r = ty; r < 32; r += 8) {
+            const int c = c0 + r;
             if (c < a.C && o < a.row_pitch)
-                dst[(((long long)c * a.d2 + i2) * a.d1 + i1) * a.row_pitch + o] = tile[tx][r];
+                dst[(((long long)c * a.d2 + i2) * a.d1 + i1) * a.row_pitch + o] =
+                    o < a.out_len ? tile[tx * a.step + j][r] : 0.f;
         }
-        __syncthreads();
     }
 }
 
@@ -369,6 +376,7 @@ extern "C" int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int3
                 "bad sizes");
     for (int i = 0; i < 3; ++i) IVX_REQUIRE(dims[i] > 0 && axes[i] >= 0 && axes[i] < 3, "bad dims / axes");
     IVX_REQUIRE(axes[0] != axes[1] && axes[0] != axes[2] && axes[1] != axes[2], "axes must be a permutation");
+    IVX_REQUIRE(31 * step + n_shifts <= ivx::CM_ROWS, "step / n_shifts too large (31 * step + n_shifts <= 96)");
     const long long st[3] = {(long long)dims[1] * dims[2] * n_channels, (long long)dims[2] * n_channels, n_channels};
     ivx::CmArgs a;
     a.x = x, a.out = out, a.C = n_channels, a.n_shifts = n_shifts, a.shift0 = shift0, a.step = step;
