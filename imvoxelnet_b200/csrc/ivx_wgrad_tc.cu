@@ -3,19 +3,23 @@
 //   dW[tap][co][ci] = sum over output voxels o of  dz[o][co] * x[o * stride - pad + tap][ci]
 //
 // is, per tap, a GEMM whose reduction runs over VOXELS.  tcgen05 wants both operands K-major in
-// shared memory, i.e. voxels contiguous: the caller hands in channel-major ("transposed") copies
-//   dz_t [batch][c_out][D2][D1][D0]     x_t [batch][c_in][I2][I1][I0]      (fp32, D0 fastest)
-// where (D0, D1, D2) is a permutation of the layer's (X, Y, Z); rows may be padded (pitches are given).
-// The TMA also wants the innermost coordinate of a swizzled box 16-byte aligned (measured: an x box
-// starting one voxel to the left is an illegal instruction), so the tap shift along the innermost axis
-// cannot be a coordinate (nor can its innermost dimension be strided): x_t holds one copy per tap
-// position along that axis, already shifted and sub-sampled by the layer stride,
-//   x_t [k0][batch][c_in][I2][I1][D0]     x_t[j][..][o] = x[..][o * stride0 - pad0 + j]   (0 outside)
-// and tap t0 reads copy t0 at the output coordinate itself.
-// A k-step is a run of 32 output voxels along D0: one 5-D TMA box load per operand puts
-// [channel rows][32 voxels] = [rows][128 bytes] tiles into shared memory, 128B-swizzled -- the same
-// K-major layout the forward kernel feeds to the MMA.  The x box starts at o * stride - pad + tap with
-// the layer stride as the TMA's element stride, so padding and ragged borders are the TMA's zero fill.
+// shared memory, i.e. voxels contiguous, so the caller hands in "tiled channel-major" copies
+// (ivx_channel_major_ndhwc writes them): with (D0, D1, D2) a permutation of the layer's (X, Y, Z),
+//   dz_t [batch][D2][D1][D0 / 32][c_out][32]
+//   x_t  [k0][batch][I2 + 2 pad2][I1][D0 / 32][c_in][32]
+// i.e. runs of 32 voxels along D0, and all channels of a run next to each other: the operand tile of
+// a k-step ([channel rows][32 voxels] = [rows][128 bytes], the K-major swizzled layout the forward
+// kernel feeds to the MMA) is ONE contiguous block of 8..32 KB in memory.  (A plain [C][voxels]
+// layout works too but reads one 128-byte row from each of c_in + c_out planes per k-step: 27 %
+// tensor-pipe activity and 2.3 TB/s of scattered DRAM reads in ncu.)
+// Two TMA rules found by measurement shape x_t: a swizzled box cannot start at an innermost coordinate
+// that is not 16-byte aligned (an x box starting one voxel to the left is an illegal instruction) and
+// the innermost dimension cannot be strided, so the tap shift and the layer stride along D0 are baked
+// into one copy of x per tap position along that axis,
+//   x_t[j][..][o] = x[..][o * stride0 - pad0 + j]      (0 outside the volume),
+// indexed by OUTPUT coordinate.  The shift along D1 is a TMA coordinate (zero fill outside); the planes
+// along D2 are merged with the batch into one TMA dimension, so x_t carries pad2 zero planes on
+// either side of every volume instead.
 // One CTA owns (a group of taps, 128 output channels, up to 256 input channels, a slice of the voxel
 // range): warp 0 issues the loads, warp 1 the MMAs (M = 128 rows of c_out, N = c_in tile, K = 8 per
 // instruction, one fp32 accumulator per tap in TMEM), warps 2..5 add the accumulators into dW with
@@ -41,6 +45,7 @@ struct WgArgs {
     long long steps_per_split;
     int stages;
     int a_rows;                      // rows of the grad_z box: min(c_out, 128)
+    int dz_planes, x_planes;         // planes per volume along D2 in dz_t, and in x_t (with its zero planes)
     int group;                       // taps along D1 handled by one CTA (kernel[1], or 1)
     int debug;                       // IVX_WG_DEBUG bits: 1 no TMA loads, 2 no MMAs, 4 no epilogue reads
     float *dw;                       // [taps (kx,ky,kz order)][c_out][c_in]
@@ -98,7 +103,7 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
                 int t = a.div_c0.divmod((int)ks, r0);
                 t = a.div_c1.divmod(t, r1);
                 const int b = a.div_c2.divmod(t, r2);
-                const int o0 = r0 * a.box[0], o1 = r1 * a.box[1], o2 = r2 * a.box[2];
+                const int o1 = r1, o2 = r2;      // (r0 counts runs of 32 voxels along D0)
                 mbar_wait(smem_u32(empty_bar + stage), phase ^ 1);
                 const uint32_t bar = smem_u32(full_bar + stage);
                 const uint32_t sa = smem_u32(smem + (size_t)stage * stage_bytes);
@@ -108,12 +113,12 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
                     // a box always arrives in full, whatever part of it lies outside the tensor
                     mbar_expect_tx(bar, (uint32_t)(((a.debug & 8) ? 0 : a.a_rows * 128) +
                                                    ((a.debug & 16) ? 0 : a.group * b_bytes)));
-                    if (!(a.debug & 8)) tma_load_5d(sa, &map_dz, bar, o0, o1, o2, co_t * 128, b);
+                    if (!(a.debug & 8)) tma_load_5d(sa, &map_dz, bar, 0, co_t * 128, r0, o1, b * a.dz_planes + o2);
                     if (!(a.debug & 16))
                         for (int g = 0; g < a.group; ++g)
-                            tma_load_5d(sa + WG_A_BYTES + g * b_bytes, &map_x, bar, o0,
-                                        o1 * a.stride[1] - a.pad[1] + t1_lo + g, o2 * a.stride[2] - a.pad[2] + t2,
-                                        ci_t * a.n_tile, t0 * a.batch + b);
+                            tma_load_5d(sa + WG_A_BYTES + g * b_bytes, &map_x, bar, 0, ci_t * a.n_tile, r0,
+                                        o1 * a.stride[1] - a.pad[1] + t1_lo + g,
+                                        (t0 * a.batch + b) * a.x_planes + o2 * a.stride[2] + t2);
                 }
                 if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
             }
@@ -213,18 +218,15 @@ extern "C" int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *p, int32_t *a
     return IVX_OK;
 }
 
-extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float *x_t, const int64_t *x_pitch,
-                                        const float *dz_t, const int64_t *dz_pitch, float *grad_w, void *stream) {
-    IVX_REQUIRE(p && x_t && dz_t && grad_w && x_pitch && dz_pitch, "NULL argument");
+extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float *x_t, const float *dz_t,
+                                        float *grad_w, void *stream) {
+    IVX_REQUIRE(p && x_t && dz_t && grad_w, "NULL argument");
     int32_t axes[3];
     int rc = ivx_conv3d_wgrad_tf32_axes(p, axes);
     if (rc != IVX_OK) return rc;
     IVX_REQUIRE((reinterpret_cast<uintptr_t>(x_t) | reinterpret_cast<uintptr_t>(dz_t) |
                  reinterpret_cast<uintptr_t>(grad_w)) % 16 == 0,
                 "tensors must be 16-byte aligned");
-    for (int i = 0; i < 4; ++i)
-        IVX_REQUIRE(x_pitch[i] > 0 && dz_pitch[i] > 0 && x_pitch[i] % 4 == 0 && dz_pitch[i] % 4 == 0,
-                    "pitches must be positive multiples of 4 elements (16 bytes)");
     WgArgs a;
     int axis[3];
     plan_wgrad(p, axis, a.box);
@@ -271,31 +273,28 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
     if (a.stages > 8) a.stages = 8;
     const size_t smem = (size_t)a.stages * stage_bytes + 2048;
 
+    a.dz_planes = p->out_dims[axis[2]];
+    a.x_planes = p->in_dims[axis[2]] + 2 * p->pad[axis[2]];
+    const CUtensorMapDataType dt = (a.debug & 32) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32;
+    const cuuint64_t n_runs = (cuuint64_t)a.chunks[0];
+    const cuuint32_t es[5] = {1, 1, 1, 1, 1};
     alignas(64) CUtensorMap map_dz, map_x;
-    {
-        const cuuint64_t dims[5] = {(cuuint64_t)p->out_dims[axis[0]], (cuuint64_t)p->out_dims[axis[1]],
-                                    (cuuint64_t)p->out_dims[axis[2]], (cuuint64_t)p->c_out, (cuuint64_t)p->batch};
-        const cuuint64_t st[4] = {(cuuint64_t)dz_pitch[0] * 4, (cuuint64_t)dz_pitch[1] * 4, (cuuint64_t)dz_pitch[2] * 4,
-                                  (cuuint64_t)dz_pitch[3] * 4};
-        const cuuint32_t box[5] = {(cuuint32_t)a.box[0], (cuuint32_t)a.box[1], (cuuint32_t)a.box[2],
-                                   (cuuint32_t)(p->c_out < 128 ? p->c_out : 128), 1};
-        const cuuint32_t es[5] = {1, 1, 1, 1, 1};
-        rc = encode_map_sw128(&map_dz, (a.debug & 32) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 5, const_cast<float *>(dz_t), dims, st, box,
-                              es, "grad_z (channel-major)");
+    {   // (voxel in run, channel, run along D0, D1, plane x batch)
+        const cuuint64_t dims[5] = {32, (cuuint64_t)p->c_out, n_runs, (cuuint64_t)p->out_dims[axis[1]],
+                                    (cuuint64_t)a.dz_planes * p->batch};
+        cuuint64_t st[4] = {128, (cuuint64_t)p->c_out * 128, 0, 0};
+        st[2] = st[1] * n_runs, st[3] = st[2] * p->out_dims[axis[1]];
+        const cuuint32_t box[5] = {32, (cuuint32_t)a.a_rows, 1, 1, 1};
+        rc = encode_map_sw128(&map_dz, dt, 5, const_cast<float *>(dz_t), dims, st, box, es, "grad_z (tiled channel-major)");
         if (rc != IVX_OK) return rc;
     }
-    {
-        // innermost: the OUTPUT extent (the copies are indexed by output coordinate); outermost: copy x batch
-        const cuuint64_t dims[5] = {(cuuint64_t)p->out_dims[axis[0]], (cuuint64_t)p->in_dims[axis[1]],
-                                    (cuuint64_t)p->in_dims[axis[2]], (cuuint64_t)p->c_in,
-                                    (cuuint64_t)p->batch * p->kernel[axis[0]]};
-        const cuuint64_t st[4] = {(cuuint64_t)x_pitch[0] * 4, (cuuint64_t)x_pitch[1] * 4, (cuuint64_t)x_pitch[2] * 4,
-                                  (cuuint64_t)x_pitch[3] * 4};
-        const cuuint32_t box[5] = {(cuuint32_t)a.box[0], (cuuint32_t)(a.box[1] * a.stride[1]),
-                                   (cuuint32_t)(a.box[2] * a.stride[2]), (cuuint32_t)a.n_tile, 1};
-        const cuuint32_t es[5] = {1, (cuuint32_t)a.stride[1], (cuuint32_t)a.stride[2], 1, 1};
-        rc = encode_map_sw128(&map_x, (a.debug & 32) ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_TFLOAT32, 5, const_cast<float *>(x_t), dims, st, box, es,
-                              "x (channel-major)");
+    {   // the same for x, with one copy per tap position along D0 and the zero planes along D2
+        const cuuint64_t dims[5] = {32, (cuuint64_t)p->c_in, n_runs, (cuuint64_t)p->in_dims[axis[1]],
+                                    (cuuint64_t)a.x_planes * p->batch * p->kernel[axis[0]]};
+        cuuint64_t st[4] = {128, (cuuint64_t)p->c_in * 128, 0, 0};
+        st[2] = st[1] * n_runs, st[3] = st[2] * p->in_dims[axis[1]];
+        const cuuint32_t box[5] = {32, (cuuint32_t)a.n_tile, 1, 1, 1};
+        rc = encode_map_sw128(&map_x, dt, 5, const_cast<float *>(x_t), dims, st, box, es, "x (tiled channel-major)");
         if (rc != IVX_OK) return rc;
     }
     rc = check_cuda(cudaFuncSetAttribute(conv3d_wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -308,11 +307,13 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
 }
 
 // ---------------------------------------------------------------------------------------------
-// Channel-major copies for the weight-gradient kernel: x [batch][X][Y][Z][C] (channels-last) ->
-//   out [n_shifts][batch][C][D2][D1][row_pitch]     out[j][..][o] = x[..][o * step + shift0 + j] along axis D0
-// (zero where o + shift is outside the volume, and in the padding o >= out_len of every row).
+// Tiled channel-major copies for the weight-gradient kernel: x [batch][X][Y][Z][C] (channels-last) ->
+//   out [n_shifts][batch][D2 + 2 halo][D1][runs][C][32]
+//   out[j][b][i2 + halo][i1][o / 32][c][o % 32] = x[b][..][c] at position o * step + shift0 + j along D0
+// (zero where that position is outside the volume, for o >= out_len, and in the halo planes).
 // 32 x 32 tiles of (position along D0, channel) go through shared memory: reads are contiguous
-// along channels, writes along D0; the shifted copies re-read the same lines from L1/L2.
+// along channels, a tile is written as one contiguous 4 KB block; the source rows are staged once
+// for all shifted copies.
 // ---------------------------------------------------------------------------------------------
 namespace ivx {
 
@@ -322,46 +323,47 @@ struct CmArgs {
     int C, n_shifts, shift0, step;
     int d0, d1, d2;                  // input extents along the permuted axes
     long long s0, s1, s2, sb;        // element strides of those axes (and of the batch) in x
-    int out_len, row_pitch;          // valid positions and allocated length of an output row
-    int o_tiles;
-    long long lines;                 // batch * d2 * d1
+    int out_len, halo, batch;
+    int o_tiles;                     // runs of 32 output positions
 };
 
 constexpr int CM_ROWS = 96;          // source positions one block stages: 31 * step + n_shifts of them
 
 __global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
     __shared__ float tile[CM_ROWS][33];
+    const int planes = a.d2 + 2 * a.halo;
     const long long blk = blockIdx.x;
     const int ot = (int)(blk % a.o_tiles);
     const long long line = blk / a.o_tiles;
     const int i1 = (int)(line % a.d1);
     const long long t = line / a.d1;
-    const int i2 = (int)(t % a.d2), b = (int)(t / a.d2);
+    const int i2h = (int)(t % planes), b = (int)(t / planes);
+    const int i2 = i2h - a.halo;
+    const bool real_plane = i2 >= 0 && i2 < a.d2;
     const int c0 = blockIdx.y * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8 threads
-    const float *src = a.x + b * a.sb + i2 * a.s2 + i1 * a.s1;
-    const int batch = (int)(a.lines / ((long long)a.d1 * a.d2));
-    // every source position the 32 outputs of this tile need, for all shifts, read once:
-    // rows = positions, columns = channels (coalesced reads)
-    const int i_lo = ot * 32 * a.step + a.shift0;
-    const int n_rows = 31 * a.step + a.n_shifts;
-    for (int r = ty; r < n_rows; r += 8) {
-        const int i = i_lo + r;
-        float v = 0.f;
-        if (i >= 0 && i < a.d0 && c0 + tx < a.C) v = __ldg(src + i * a.s0 + c0 + tx);
-        tile[r][tx] = v;
+    if (real_plane) {
+        // every source position the 32 outputs of this tile need, for all shifts, read once:
+        // rows = positions, columns = channels (coalesced reads)
+        const float *src = a.x + b * a.sb + i2 * a.s2 + i1 * a.s1;
+        const int i_lo = ot * 32 * a.step + a.shift0;
+        const int n_rows = 31 * a.step + a.n_shifts;
+        for (int r = ty; r < n_rows; r += 8) {
+            const int i = i_lo + r;
+            float v = 0.f;
+            if (i >= 0 && i < a.d0 && c0 + tx < a.C) v = __ldg(src + i * a.s0 + c0 + tx);
+            tile[r][tx] = v;
+        }
     }
     __syncthreads();
-    // rows = channels, columns = output positions (coalesced writes), one pass per shifted copy
+    // rows = channels, columns = output positions: 32 x 128 contiguous bytes per tile and copy
     const int o = ot * 32 + tx;
     for (int j = 0; j < a.n_shifts; ++j) {
-        float *dst = a.out + ((((long long)j * batch + b) * a.C) * a.d2 * a.d1) * a.row_pitch;
+        float *dst = a.out + ((((((long long)j * a.batch + b) * planes + i2h) * a.d1 + i1) * a.o_tiles + ot) * a.C) * 32;
 #pragma unroll
         for (int r = ty; r < 32; r += 8) {
             const int c = c0 + r;
-            if (c < a.C && o < a.row_pitch)
-                dst[(((long long)c * a.d2 + i2) * a.d1 + i1) * a.row_pitch + o] =
-                    o < a.out_len ? tile[tx * a.step + j][r] : 0.f;
+            if (c < a.C) dst[c * 32 + tx] = (real_plane && o < a.out_len) ? tile[tx * a.step + j][r] : 0.f;
         }
     }
 }
@@ -370,10 +372,9 @@ __global__ void __launch_bounds__(256) channel_major_kernel(const CmArgs a) {
 
 extern "C" int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int32_t *dims, int32_t n_channels,
                                        const int32_t *axes, int32_t n_shifts, int32_t shift0, int32_t step,
-                                       int32_t out_len, int32_t row_pitch, float *out, void *stream) {
+                                       int32_t out_len, int32_t halo, float *out, void *stream) {
     IVX_REQUIRE(x && dims && axes && out, "NULL argument");
-    IVX_REQUIRE(batch > 0 && n_channels > 0 && n_shifts > 0 && step > 0 && out_len > 0 && row_pitch >= out_len,
-                "bad sizes");
+    IVX_REQUIRE(batch > 0 && n_channels > 0 && n_shifts > 0 && step > 0 && out_len > 0 && halo >= 0, "bad sizes");
     for (int i = 0; i < 3; ++i) IVX_REQUIRE(dims[i] > 0 && axes[i] >= 0 && axes[i] < 3, "bad dims / axes");
     IVX_REQUIRE(axes[0] != axes[1] && axes[0] != axes[2] && axes[1] != axes[2], "axes must be a permutation");
     IVX_REQUIRE(31 * step + n_shifts <= ivx::CM_ROWS, "step / n_shifts too large (31 * step + n_shifts <= 96)");
@@ -382,10 +383,9 @@ extern "C" int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int3
     a.x = x, a.out = out, a.C = n_channels, a.n_shifts = n_shifts, a.shift0 = shift0, a.step = step;
     a.d0 = dims[axes[0]], a.d1 = dims[axes[1]], a.d2 = dims[axes[2]];
     a.s0 = st[axes[0]], a.s1 = st[axes[1]], a.s2 = st[axes[2]], a.sb = st[0] * dims[0];
-    a.out_len = out_len, a.row_pitch = row_pitch;
-    a.o_tiles = (row_pitch + 31) / 32;
-    a.lines = (long long)batch * a.d2 * a.d1;
-    const long long blocks = a.lines * a.o_tiles;
+    a.out_len = out_len, a.halo = halo, a.batch = batch;
+    a.o_tiles = (out_len + 31) / 32;
+    const long long blocks = (long long)batch * (a.d2 + 2 * halo) * a.d1 * a.o_tiles;
     IVX_REQUIRE(blocks < (1ll << 31), "too many voxels");
     dim3 grid((unsigned)blocks, (unsigned)((n_channels + 31) / 32));
     ivx::channel_major_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);

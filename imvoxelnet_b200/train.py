@@ -68,20 +68,21 @@ def _conv_tf32(fc, params, x, w_tc, bias, y):
           ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
 
 
-def _channel_major(t, axes, shifts=None, out_len=None, step=1):
-    """[B, X, Y, Z, C] -> dense [n, B, C, D2, D1, Lp] with D_i = axis axes[i], rows padded to 4 elements, and
-    the element pitches of dimensions 1..4 (what ivx_conv3d_wgrad_tf32_tc takes).  Copy j holds
-    ``t[.., o * step + shifts[j]]`` at ``o < out_len`` (zero outside the volume); default: one plain copy."""
+def _channel_major(t, axes, shifts=None, out_len=None, step=1, halo=0):
+    """[B, X, Y, Z, C] -> [n, B, D2 + 2 halo, D1, runs, C, 32]: the tiled channel-major operand layout of
+    ivx_conv3d_wgrad_tf32_tc (D_i = axis axes[i]; runs of 32 positions along D0).  Copy j holds
+    ``t[.., o * step + shifts[j]]`` at ``o < out_len`` (zero outside the volume and in the halo planes);
+    default: one plain copy."""
     assert t.is_contiguous() and t.dtype == torch.float32
     b, dims, c = t.shape[0], tuple(t.shape[1:4]), t.shape[4]
     shifts = shifts or [0]
     out_len = out_len or dims[axes[0]]
-    pitch = -(-out_len // 4) * 4
     d1, d2 = dims[axes[1]], dims[axes[2]]
-    out = torch.empty((len(shifts), b, c, d2, d1, pitch), dtype=torch.float32, device=t.device)
+    out = torch.empty((len(shifts), b, d2 + 2 * halo, d1, -(-out_len // 32), c, 32), dtype=torch.float32,
+                      device=t.device)
     _call("ivx_channel_major_ndhwc", t.data_ptr(), b, _lib.i32(dims), c, _lib.i32(axes), len(shifts), shifts[0],
-          step, out_len, pitch, out.data_ptr())
-    return out, _lib.i64([pitch, pitch * d1, pitch * d1 * d2, c * pitch * d1 * d2])
+          step, out_len, halo, out.data_ptr())
+    return out
 
 
 def _wgrad_tf32(p, x, dz):
@@ -106,9 +107,9 @@ def _wgrad_tf32(p, x, dz):
     if PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-    x_t, x_pitch = _channel_major(src, axes, shifts=[j - q.pad[a0] for j in range(q.kernel[a0])],
-                                  out_len=q.out_dims[a0], step=q.stride[a0])
-    dz_t, dz_pitch = _channel_major(grad, axes)
+    x_t = _channel_major(src, axes, shifts=[j - q.pad[a0] for j in range(q.kernel[a0])],
+                         out_len=q.out_dims[a0], step=q.stride[a0], halo=q.pad[axes[2]])
+    dz_t = _channel_major(grad, axes)
     if PROFILE is not None:
         e1.record()
         torch.cuda.synchronize()
@@ -117,7 +118,7 @@ def _wgrad_tf32(p, x, dz):
         rec[1] += e0.elapsed_time(e1)
     k = tuple(q.kernel)
     dw = torch.zeros((k[0], k[1], k[2], q.c_out, q.c_in), dtype=torch.float32, device=x.device)
-    _call("ivx_conv3d_wgrad_tf32_tc", q, x_t.data_ptr(), x_pitch, dz_t.data_ptr(), dz_pitch, dw.data_ptr())
+    _call("ivx_conv3d_wgrad_tf32_tc", q, x_t.data_ptr(), dz_t.data_ptr(), dw.data_ptr())
     if p.transposed:
         return dw.permute(3, 4, 0, 1, 2)    # [k][k][k][Cin_T][Cout_T] -> torch's [Cin_T, Cout_T, kX, kY, kZ]
     return dw.permute(3, 4, 0, 1, 2)        # torch's [Cout, Cin, kX, kY, kZ]

@@ -450,35 +450,35 @@ IVX_API int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *params, const
  * convolution from its output grid to its input grid with the roles of x and grad_z exchanged):
  *   grad_w[tap][c_out][c_in] += sum_o grad_z[o][c_out] * x[o * stride - pad + tap][c_in]
  * (taps in kX, kY, kZ order; grad_w fp32, zero-filled by the caller; fp32 vector reductions).
- * The reduction runs over voxels, so both operands are taken CHANNEL-MAJOR:
- *   dz_t [batch][c_out][D2][D1][D0]      x_t [k0][batch][c_in][I2][I1][D0]
+ * The reduction runs over voxels, so both operands are taken in the TILED CHANNEL-MAJOR layout that
+ * ivx_channel_major_ndhwc writes (runs of 32 voxels along D0, all channels of a run adjacent):
+ *   dz_t [batch][D2][D1][ceil(D0 / 32)][c_out][32]
+ *   x_t  [k0][batch][I2 + 2 pad2][I1][ceil(D0 / 32)][c_in][32]
  * where permuted axis i is axis axes[i] of (X, Y, Z) as returned by ivx_conv3d_wgrad_tf32_axes,
- * D = out_dims and I = in_dims in that order, and k0 = kernel[axes[0]].  x_t holds one copy of x
- * per tap position along the innermost axis, already shifted and sub-sampled:
+ * D = out_dims and I = in_dims in that order, k0 = kernel[axes[0]], pad2 = pad[axes[2]].  x_t holds
+ * one copy of x per tap position along D0, shifted and sub-sampled and indexed by OUTPUT coordinate:
  * x_t[j][..][o] = x[..][o * stride[axes[0]] - pad[axes[0]] + j], zero outside the volume (the TMA
  * can neither stride the innermost dimension nor start a swizzled box at an unaligned innermost
- * coordinate, so that shift cannot be a coordinate; the shifts along the other two axes are).  x_pitch / dz_pitch: host[4], element
- * pitches of dimensions 1..4 (row, plane, channel, batch), multiples of 4 -- rows may be padded;
- * the copies of x_t follow each other at batch * x_pitch[3].
+ * coordinate), and pad2 zero planes on either side of every volume along D2.
  * IVX_ERR_UNSUPPORTED for other layers (callers use ivx_conv3d_wgrad_ndhwc).
  */
 /*
- * ivx_channel_major_ndhwc -- the operand copies ivx_conv3d_wgrad_tf32_tc takes, from a channels-last
- * tensor x [batch][X][Y][Z][C] (dims = {X, Y, Z}):
- *   out [n_shifts][batch][C][D2][D1][row_pitch],  out[j][..][o] = x[..][o * step + shift0 + j]
- * along axis D0, with D_i = axis axes[i]; zero where the source index falls outside the volume and
- * for o >= out_len.  grad_z: n_shifts = 1, shift0 = 0, step = 1, out_len = its extent along D0.
+ * ivx_channel_major_ndhwc -- those operand copies, from a channels-last tensor
+ * x [batch][X][Y][Z][C] (dims = {X, Y, Z}), D_i = axis axes[i]:
+ *   out [n_shifts][batch][D2 + 2 halo][D1][ceil(out_len / 32)][C][32]
+ *   out[j][b][i2 + halo][i1][o / 32][c][o % 32] = x[b][..][c] at position o * step + shift0 + j along D0
+ * zero where that position is outside the volume, for o >= out_len and in the halo planes.
+ * grad_z: n_shifts = 1, shift0 = 0, step = 1, out_len = its extent along D0, halo = 0.
  * x: n_shifts = kernel[axes[0]], shift0 = -pad[axes[0]], step = stride[axes[0]],
- * out_len = out_dims[axes[0]].
+ * out_len = out_dims[axes[0]], halo = pad[axes[2]].
  */
 IVX_API int ivx_channel_major_ndhwc(const float *x, int32_t batch, const int32_t *dims /* host[3] */,
                                     int32_t n_channels, const int32_t *axes /* host[3] */, int32_t n_shifts,
-                                    int32_t shift0, int32_t step, int32_t out_len, int32_t row_pitch,
-                                    float *out, void *stream);
+                                    int32_t shift0, int32_t step, int32_t out_len, int32_t halo, float *out,
+                                    void *stream);
 IVX_API int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *params, int32_t *axes /* host[3] */);
-IVX_API int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *params, const float *x_t,
-                                     const int64_t *x_pitch /* host[4] */, const float *dz_t,
-                                     const int64_t *dz_pitch /* host[4] */, float *grad_w, void *stream);
+IVX_API int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *params, const float *x_t, const float *dz_t,
+                                     float *grad_w, void *stream);
 
 /* grad_x [batch][X][Y][Z][C] += transpose of ivx_upsample2x_trilinear_ndhwc applied to grad_y
  * [batch][2X][2Y][2Z][C]; grad_x must be zero-filled by the caller */
