@@ -26,6 +26,7 @@ def main():
     ap.add_argument("--transposed", action="store_true")
     ap.add_argument("--residual", action="store_true")
     ap.add_argument("--reps", type=int, default=5)
+    ap.add_argument("--precision", default="bf16", choices=["bf16", "tf32"])
     args = ap.parse_args()
     dev = "cuda:0"
     torch.manual_seed(0)
@@ -35,8 +36,10 @@ def main():
         c = nn.Conv3d(args.cin, args.cout, args.kernel, args.stride, args.kernel // 2, bias=False)
     bn = nn.BatchNorm3d(args.cout)
     layer = conv.FusedConv(c.to(dev).eval(), bn.to(dev).eval(), relu=True)
-    x = torch.randn((args.batch, *args.dims, args.cin), device=dev).to(torch.bfloat16)
-    with torch.no_grad():
+    x = torch.randn((args.batch, *args.dims, args.cin), device=dev)
+    if args.precision == "bf16":
+        x = x.to(torch.bfloat16)
+    with torch.no_grad(), conv.tf32(args.precision == "tf32"):
         y = layer(x)
         res = torch.randn_like(y) if args.residual else None
         for _ in range(2):
@@ -51,7 +54,7 @@ def main():
     ms = e0.elapsed_time(e1) / args.reps
     taps = args.kernel ** 3
     rows = (x.numel() // args.cin) if args.transposed else (y.numel() // args.cout)
-    nbytes = (x.numel() + y.numel() * (2 if args.residual else 1)) * 2
+    nbytes = (x.numel() + y.numel() * (2 if args.residual else 1)) * x.element_size()
     print(json.dumps({"ms": ms, "tflops": 2.0 * rows * args.cin * args.cout * taps / ms / 1e9,
                       "gbytes_per_s": nbytes / ms / 1e6, "args": vars(args)}))
 
