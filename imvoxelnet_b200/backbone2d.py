@@ -9,7 +9,6 @@ dicts still build and ``extract_feat`` can run end to end on synthetic
 images.  They are plain PyTorch (torchvision ResNet, a textbook FPN) and make
 no attempt at being fast.
 """
-import torch
 import torch.nn.functional as F
 from torch import nn
 
