@@ -242,10 +242,12 @@ __device__ __forceinline__ void add4(float4 (&acc)[CPL], const float4 (&r)[CPL])
     }
 }
 
-// sum / count (count converted to float, :72; 0 where unseen, :74), then store
+// sum / count (count converted to float, :72; 0 where unseen, :74), then store.  Called by all lanes
+// of the warp (`active` = this lane's voxel exists): one variant exchanges data between lanes.
 template <int G, int CPL, bool DIVIDE, typename OutT, bool FB>
 __device__ __forceinline__ void finish_voxel(const BpArgs &a, OutT *vol, int n, int t, int cnt,
-                                             float4 (&acc)[CPL * (FB ? 2 : 1)], const bool (&ch_ok)[CPL]) {
+                                             float4 (&acc)[CPL * (FB ? 2 : 1)], const bool (&ch_ok)[CPL],
+                                             bool active) {
     constexpr int NF = FB ? 2 : 1;   // float4 per 16-byte feature unit
     if (DIVIDE && a.reduce == IVX_REDUCE_MEAN && cnt > 1) {
         const float c = (float)cnt;
@@ -258,6 +260,26 @@ __device__ __forceinline__ void finish_voxel(const BpArgs &a, OutT *vol, int n, 
         }
     }  // cnt == 1: x / 1.0f == x;  cnt == 0: the accumulator is still zero
     OutT *dst = vol + (long long)n * a.os_n;
+    if constexpr (FB && sizeof(OutT) == 4) {
+        // 8 bf16 channels in, 8 fp32 channels (32 bytes) out per lane: stored as they are, every store
+        // instruction would write 16-byte pieces 32 bytes apart.  Neighbouring lanes swap halves instead,
+        // so that each instruction writes whole 32-byte sectors: the even lane of a pair stores the first
+        // half of both units, the odd lane the second half.
+        const bool odd = t & 1;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            const float4 send = odd ? acc[2 * i] : acc[2 * i + 1];
+            float4 recv;
+            recv.x = __shfl_xor_sync(0xffffffffu, send.x, 1), recv.y = __shfl_xor_sync(0xffffffffu, send.y, 1);
+            recv.z = __shfl_xor_sync(0xffffffffu, send.z, 1), recv.w = __shfl_xor_sync(0xffffffffu, send.w, 1);
+            const int unit_e = (t & ~1) + i * G;                 // unit of the even lane; the odd lane's is + 1
+            float *p = reinterpret_cast<float *>(dst) + unit_e * 8 + (odd ? 4 : 0);
+            if (active && unit_e * 8 < a.C) store4<float>(p, odd ? recv : acc[2 * i]);
+            if (active && (unit_e + 1) * 8 < a.C) store4<float>(p + 8, odd ? acc[2 * i + 1] : recv);
+        }
+        return;
+    }
+    if (!active) return;
 #pragma unroll
     for (int i = 0; i < CPL; ++i)
         if (ch_ok[i]) {
@@ -340,8 +362,7 @@ __global__ void __launch_bounds__(256, (CPL * (FB ? 2 : 1) <= 2 ? 4 : 2)) bp_vec
                 for (int u = 0; u < WIDTH; ++u) {
                     const int j = j0 + u * VPI + g;
                     const int n = n0 + j;
-                    if (j < T && n < a.N)
-                        finish_voxel<G, CPL, false, OutT, FB>(a, vol, n, t, o[u] >= 0, r[u], ch_ok);
+                    finish_voxel<G, CPL, false, OutT, FB>(a, vol, n, t, o[u] >= 0, r[u], ch_ok, j < T && n < a.N);
                 }
             }
         } else if constexpr (MODE == MODE_WIDE) {
@@ -373,8 +394,7 @@ __global__ void __launch_bounds__(256, (CPL * (FB ? 2 : 1) <= 2 ? 4 : 2)) bp_vec
                 for (int u = 0; u < WIDTH; ++u) {
                     const int j = j0 + u * VPI + g;
                     const int n = n0 + j;
-                    if (j < T && n < a.N)
-                        finish_voxel<G, CPL, true, OutT, FB>(a, vol, n, t, cnt[u], acc[u], ch_ok);
+                    finish_voxel<G, CPL, true, OutT, FB>(a, vol, n, t, cnt[u], acc[u], ch_ok, j < T && n < a.N);
                 }
             }
             __syncwarp();  // the table is rewritten by the next tile
@@ -399,7 +419,7 @@ __global__ void __launch_bounds__(256, (CPL * (FB ? 2 : 1) <= 2 ? 4 : 2)) bp_vec
 #pragma unroll
                     for (int u = 0; u < DEPTH; ++u) add4<ACC>(acc, r[u]);  // ascending view order
                 }
-                if (active) finish_voxel<G, CPL, true, OutT, FB>(a, vol, n, t, cnt, acc, ch_ok);
+                finish_voxel<G, CPL, true, OutT, FB>(a, vol, n, t, cnt, acc, ch_ok, active);
             }
             __syncwarp();  // the table is rewritten by the next tile
         }
