@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libivx.so")
 
-IVX_F32, IVX_BF16, IVX_U8 = 0, 1, 2
+IVX_F32, IVX_BF16, IVX_U8, IVX_F32X2 = 0, 1, 2, 3
 IVX_REDUCE_MEAN, IVX_REDUCE_PARTIAL = 0, 1
 IVX_MAX_VIEWS = 1024
 
@@ -68,6 +68,8 @@ PROTOTYPES["ivx_conv3d_ndhwc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p
                                   c_void_p]
 PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"] = PROTOTYPES["ivx_conv3d_ndhwc"][:7] + [c_void_p, c_int64, c_void_p]
 PROTOTYPES["ivx_conv3d_ndhwc_tf32_tc"] = PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"]
+PROTOTYPES["ivx_conv3d_ndhwc_f32x3_tc"] = PROTOTYPES["ivx_conv3d_ndhwc_bf16_tc"]
+PROTOTYPES["ivx_split_tf32_ndhwc"] = [c_void_p, c_void_p, c_int64, c_int, c_void_p]
 PROTOTYPES["ivx_conv3d_tc_workspace_bytes"] = [_ConvP]
 c_float = ctypes.c_float
 PROTOTYPES["ivx_channel_moments_ndhwc"] = [c_void_p, c_void_p, c_int64, c_int, c_void_p, c_void_p]

@@ -14,13 +14,17 @@ from . import _lib
 
 import contextlib
 
-__all__ = ["FusedConv", "upsample2x_trilinear", "to_ndhwc", "from_ndhwc", "launch_count", "tf32"]
+__all__ = ["FusedConv", "upsample2x_trilinear", "to_ndhwc", "from_ndhwc", "launch_count", "tf32", "fp32x3",
+           "split_tf32"]
 
 _launches = 0
 #: bf16 layers with c_in, c_out multiples of 64 run on tcgen05; False forces the CUDA-core kernel
 USE_TENSOR_CORES = True
 _DT = {torch.float32: _lib.IVX_F32, torch.bfloat16: _lib.IVX_BF16}
 _TF32 = False
+#: fp32 layers with c_in % 32 == 0 and c_out % 64 == 0 run on tcgen05 as three tf32 products ("3xTF32",
+#: ``ivx_conv3d_ndhwc_f32x3_tc``): fp32-grade results (1e-5).  False keeps them on the CUDA-core kernel.
+_FP32X3 = True
 
 
 @contextlib.contextmanager
@@ -34,6 +38,36 @@ def tf32(enabled=True):
         yield
     finally:
         _TF32 = old
+
+
+@contextlib.contextmanager
+def fp32x3(enabled=True):
+    """Inside: whether eligible fp32 layers take the 3xTF32 tensor-core kernel (the default) or the
+    CUDA-core kernel (``enabled=False``; the necks' ``precision = "fp32_simt"``)."""
+    global _FP32X3
+    old, _FP32X3 = _FP32X3, bool(enabled)
+    try:
+        yield
+    finally:
+        _FP32X3 = old
+
+
+def _rna_tf32(t):
+    """Round an fp32 tensor to tf32 (nearest, ties away from zero: PTX ``cvt.rna.tf32.f32``)."""
+    return ((t.contiguous().view(torch.int32) + 0x1000) & -0x2000).view(torch.float32)
+
+
+def split_tf32(x):
+    """[..., C] fp32 -> [..., 2C]: (hi | lo) tf32 halves with hi + lo == x up to 2^-22 (``ivx_split_tf32_ndhwc``)."""
+    global _launches
+    assert x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+    c = x.shape[-1]
+    y = torch.empty(x.shape[:-1] + (2 * c,), dtype=torch.float32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(_lib.lib().ivx_split_tf32_ndhwc(x.data_ptr(), y.data_ptr(), x.numel() // c, c, _stream()),
+                   "ivx_split_tf32_ndhwc")
+    _launches += 1
+    return y
 
 
 def launch_count():
@@ -71,6 +105,7 @@ class FusedConv:
         self._packed = None
         self._packed_tc = None
         self._packed_tf32 = None
+        self._packed_x3 = None
         self._ws = {}
 
     # ---- parameter packing (cached until a parameter or buffer changes) ----
@@ -102,7 +137,7 @@ class FusedConv:
                 elif bias is not None:
                     shift = bias.detach().to(device, torch.float32).contiguous()
             self._packed = (key, wp, scale, shift)
-            self._packed_tc = self._packed_tf32 = None
+            self._packed_tc = self._packed_tf32 = self._packed_x3 = None
         return self._packed[1:]
 
     def packed_tc(self, device):
@@ -128,6 +163,22 @@ class FusedConv:
                 self._packed_tf32 = w.permute(*perm).contiguous()
         return self._packed_tf32, scale, shift
 
+    def packed_x3(self, device):
+        """(hi | lo) tf32 halves of the weights for the 3xTF32 kernel: rows of the tensor-core layout
+        ([c_out] x taps*c_in, transposed layers [taps*c_out] x c_in), each as [2][row]."""
+        _, scale, shift = self.packed(device)
+        if self._packed_x3 is None:
+            with torch.no_grad():
+                w = self.conv.weight.detach().to(device=device, dtype=torch.float32)
+                if self.transposed:
+                    rows = w.permute(2, 3, 4, 1, 0).reshape(-1, w.shape[0])
+                else:
+                    rows = w.permute(0, 2, 3, 4, 1).reshape(w.shape[0], -1)
+                hi = _rna_tf32(rows)
+                lo = _rna_tf32(rows - hi)
+                self._packed_x3 = torch.stack([hi, lo], dim=1).contiguous()
+        return self._packed_x3, scale, shift
+
     def _workspace(self, params, device):
         """Split-K scratch of this layer for this geometry: zero-filled once, the kernel
         leaves it zero-filled (include/ivx.h); None when the layer does not split."""
@@ -150,6 +201,12 @@ class FusedConv:
         if self.transposed and residual is not None:
             return False
         return (_TF32 and x.dtype == torch.float32 and out_dtype == torch.float32
+                and self.conv.in_channels % 32 == 0 and self.conv.out_channels % 64 == 0)
+
+    def x3_eligible(self, x, out_dtype, residual=None):
+        if self.transposed and residual is not None:
+            return False
+        return (_FP32X3 and not _TF32 and x.dtype == torch.float32 and out_dtype == torch.float32
                 and self.conv.in_channels % 32 == 0 and self.conv.out_channels % 64 == 0)
 
     def out_dims(self, in_dims):
@@ -214,6 +271,16 @@ class FusedConv:
                     shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(),
                     ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
                     _stream()), "ivx_conv3d_ndhwc_tf32_tc")
+            elif self.x3_eligible(x, out_dtype, residual):
+                wt, scale, shift = self.packed_x3(x.device)
+                xs = split_tf32(x)
+                p.in_dtype = _lib.IVX_F32X2
+                ws = self._workspace(p, x.device)
+                _lib.check(_lib.lib().ivx_conv3d_ndhwc_f32x3_tc(
+                    p, xs.data_ptr(), wt.data_ptr(), scale.data_ptr() if scale is not None else None,
+                    shift.data_ptr() if shift is not None else None, res_ptr, y.data_ptr(),
+                    ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
+                    _stream()), "ivx_conv3d_ndhwc_f32x3_tc")
             else:
                 _lib.check(_lib.lib().ivx_conv3d_ndhwc(
                     p, x.data_ptr(), wp.data_ptr(), scale.data_ptr() if scale is not None else None,

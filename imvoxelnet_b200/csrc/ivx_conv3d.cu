@@ -467,6 +467,47 @@ extern "C" int ivx_upsample2x_trilinear_ndhwc(const void *x, void *y, int batch,
     return IVX_OK;
 }
 
+// fp32 -> (hi | lo) tf32 halves for the 3xTF32 layers: hi = x rounded to tf32 (10 explicit mantissa
+// bits; cvt.rna), lo = x - hi (exact in fp32) rounded to tf32 as well, so neither the TMA nor the MMA
+// unit can change a bit of what is stored.  Row r of y is [hi(x[r][0..C)) | lo(x[r][0..C))].
+// One thread per 16 bytes of input; reads and writes are fully coalesced 128-bit accesses.
+__device__ __forceinline__ float tf32_rna(float v) {
+    uint32_t u;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(v));
+    return __uint_as_float(u);
+}
+
+__global__ void __launch_bounds__(256) split_tf32_kernel(const float4 *__restrict__ x, float4 *__restrict__ y,
+                                                          long long n_vec, int cv) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_vec;
+         i += (long long)gridDim.x * blockDim.x) {
+        const long long row = i / cv;
+        const int c = (int)(i - row * cv);
+        const float4 v = __ldcs(x + i);
+        float4 hi, lo;
+        hi.x = tf32_rna(v.x), hi.y = tf32_rna(v.y), hi.z = tf32_rna(v.z), hi.w = tf32_rna(v.w);
+        lo.x = tf32_rna(v.x - hi.x), lo.y = tf32_rna(v.y - hi.y);
+        lo.z = tf32_rna(v.z - hi.z), lo.w = tf32_rna(v.w - hi.w);
+        y[row * 2 * cv + c] = hi;
+        y[row * 2 * cv + cv + c] = lo;
+    }
+}
+
+extern "C" int ivx_split_tf32_ndhwc(const float *x, float *y, int64_t rows, int n_channels, void *stream) {
+    IVX_REQUIRE(x && y, "NULL argument");
+    IVX_REQUIRE(rows > 0 && n_channels > 0 && n_channels % 4 == 0, "channels must be a multiple of 4");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    const int cv = n_channels / 4;
+    const long long n_vec = rows * cv;
+    long long blocks = (n_vec + 255) / 256;
+    if (blocks > kNumSMs * 16) blocks = kNumSMs * 16;   // grid-stride: 16 CTAs of 256 threads per SM
+    split_tf32_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        reinterpret_cast<const float4 *>(x), reinterpret_cast<float4 *>(y), n_vec, cv);
+    IVX_CHECK_LAUNCH("split_tf32 launch");
+    return IVX_OK;
+}
+
 // Data gradient of a (non-transposed) convolution, fp32: for every input voxel, gather the output
 // gradients that used it.  Same kernel as the forward pass with the channel roles exchanged.
 extern "C" int ivx_conv3d_dgrad_ndhwc(const ivx_conv3d_params *params, const float *grad_y,

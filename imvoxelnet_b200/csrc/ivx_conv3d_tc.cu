@@ -69,6 +69,9 @@ struct TcArgs {
     int steps_per_split;
     float *ws;                  // [out tiles][128 rows][n_tile] fp32, zero on entry
     unsigned *counters;         // [out tiles], zero on entry
+    // 3xTF32 (fp32-grade results, see ivx_conv3d_tc_halo.cu): activations are (hi | lo) channels, weight
+    // rows (hi | lo) x taps x c_in; the k-steps run three passes (x_lo w_hi, x_hi w_lo, x_hi w_hi)
+    int x3;
 };
 
 struct TileCoord {
@@ -201,7 +204,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
 
     const int k_chunks = a.c_in / EK;
     const int n_taps = a.taps[0] * a.taps[1] * a.taps[2];
-    const int k_steps = n_taps * k_chunks;
+    const int pass_steps = n_taps * k_chunks;            // k-steps of one pass over (tap, chunk)
+    const int k_steps = a.x3 ? 3 * pass_steps : pass_steps;
 
     if (warp == 0) {
         // ------------------------------ TMA producer ------------------------------
@@ -211,7 +215,8 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                 const TileCoord tc = decode_tile(a, t);
                 const int k_lo = (int)(t % a.k_splits) * a.steps_per_split;
                 const int k_hi = min(k_steps, k_lo + a.steps_per_split);
-                for (int ks = k_lo; ks < k_hi; ++ks) {
+                for (int ks0 = k_lo; ks0 < k_hi; ++ks0) {
+                    const int pass = a.x3 ? ks0 / pass_steps : 0, ks = ks0 - pass * pass_steps;
                     const int tap = ks / k_chunks, kc = ks - tap * k_chunks;
                     const int kz = tap % a.taps[2], t2 = tap / a.taps[2];
                     const int ky = t2 % a.taps[1], kx = t2 / a.taps[1];
@@ -222,8 +227,11 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
                     const uint32_t bar = smem_u32(full_bar + stage);
                     const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
                     mbar_expect_tx(bar, (uint32_t)(a.box[0] * a.box[1] * a.box[2] * 128 + b_bytes));
-                    tma_load_5d(sa, &map_x, bar, kc * EK, cz, cy, cx, tc.b);
-                    tma_load_2d(sa + TC_A_BYTES, &map_w, bar, tap * a.c_in + kc * EK, tc.n0);
+                    // x3: pass 0 = (x_lo, w_hi), pass 1 = (x_hi, w_lo), pass 2 = (x_hi, w_hi)
+                    const int xch = (a.x3 && pass == 0 ? a.c_in : 0) + kc * EK;
+                    const int wcol = (a.x3 && pass == 1 ? n_taps * a.c_in : 0) + tap * a.c_in + kc * EK;
+                    tma_load_5d(sa, &map_x, bar, xch, cz, cy, cx, tc.b);
+                    tma_load_2d(sa + TC_A_BYTES, &map_w, bar, wcol, tc.n0);
                     if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
                 }
             }
@@ -512,9 +520,10 @@ using namespace ivx;
 static int validate_tc(const ivx_conv3d_params *p, bool has_residual, bool free_output = false) {
     IVX_REQUIRE(p != nullptr, "NULL params");
     const bool bf16 = p->in_dtype == IVX_BF16 && p->out_dtype == IVX_BF16;
-    const bool tf32 = p->in_dtype == IVX_F32 && p->out_dtype == IVX_F32;
+    const bool tf32 = (p->in_dtype == IVX_F32 || p->in_dtype == IVX_F32X2) && p->out_dtype == IVX_F32;
     if (!bf16 && !tf32)
-        return fail(IVX_ERR_UNSUPPORTED, "tensor-core path: bf16 in and out, or fp32 in and out (tf32 math)");
+        return fail(IVX_ERR_UNSUPPORTED,
+                    "tensor-core path: bf16 in and out, or fp32 out with fp32 (tf32 math) or split fp32 (3xTF32) in");
     if (p->c_in % (bf16 ? 64 : 32) != 0 || p->c_out % 64 != 0)
         return fail(IVX_ERR_UNSUPPORTED,
                     "tensor-core path: c_in must be a multiple of 64 (bf16) or 32 (tf32), c_out of 64");
@@ -577,7 +586,9 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     // pick the split that minimises waves x k-steps per item, charging 3% per extra split for the
     // fp32 partials that go through the L2 workspace (needs a workspace; the caller may not have
     // one -> k_splits reset to 1 later).
-    const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / (p->in_dtype == IVX_BF16 ? 64 : 32));
+    a.x3 = p->in_dtype == IVX_F32X2 ? 1 : 0;
+    const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / (p->in_dtype == IVX_BF16 ? 64 : 32)) *
+                        (a.x3 ? 3 : 1);
     a.k_splits = 1;
     a.steps_per_split = k_steps;
     {
@@ -623,7 +634,8 @@ static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weig
     TcArgs a;
     plan_tc(p, a);
     a.ws = nullptr, a.counters = nullptr;
-    const int k_steps_total = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / EK);
+    const int k_steps_total = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / EK) * (a.x3 ? 3 : 1);
+    const int cin_mem = a.x3 ? 2 * p->c_in : p->c_in;    // channels per voxel in memory (hi | lo)
     if (a.k_splits > 1) {
         const long long out_tiles = a.n_tiles / a.k_splits;
         const int64_t ws_floats = out_tiles * TC_ROWS * a.n_tile;
@@ -677,10 +689,10 @@ static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weig
 
     alignas(64) CUtensorMap map_x, map_w, map_y, map_r;
     {
-        const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[2], (cuuint64_t)p->in_dims[1],
+        const cuuint64_t dims[5] = {(cuuint64_t)cin_mem, (cuuint64_t)p->in_dims[2], (cuuint64_t)p->in_dims[1],
                                     (cuuint64_t)p->in_dims[0], (cuuint64_t)p->batch};
         cuuint64_t st[4];
-        st[0] = (cuuint64_t)p->c_in * ES;
+        st[0] = (cuuint64_t)cin_mem * ES;
         st[1] = st[0] * p->in_dims[2];
         st[2] = st[1] * p->in_dims[1];
         st[3] = st[2] * p->in_dims[0];
@@ -693,8 +705,8 @@ static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weig
     {
         // [c_out][taps * c_in] for convolutions, [taps * c_out][c_in] for transposed layers
         const int taps = p->transposed ? 1 : p->kernel[0] * p->kernel[1] * p->kernel[2];
-        const cuuint64_t dims[2] = {(cuuint64_t)taps * p->c_in, (cuuint64_t)n_total};
-        const cuuint64_t st[1] = {(cuuint64_t)taps * p->c_in * ES};
+        const cuuint64_t dims[2] = {(cuuint64_t)taps * cin_mem, (cuuint64_t)n_total};
+        const cuuint64_t st[1] = {(cuuint64_t)taps * cin_mem * ES};
         const cuuint32_t box[2] = {EK, (cuuint32_t)a.n_tile};
         const cuuint32_t es[2] = {1, 1};
         int rc = encode_map_sw128(&map_w, dt_in, 2, const_cast<void *>(weight), dims, st, box, es, "weights");
@@ -786,4 +798,25 @@ extern "C" int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *p, const f
         IVX_REQUIRE(y_strides[i] > 0 && y_strides[i] % 4 == 0, "output strides must be positive multiples of 4 elements");
     return launch_tc<true>(p, x, weight, scale, shift, nullptr, y, workspace, workspace_bytes, (cudaStream_t)stream,
                            y_strides);
+}
+
+extern "C" int ivx_conv3d_ndhwc_f32x3_tc(const ivx_conv3d_params *p, const float *x_split, const float *weight_split,
+                                         const float *scale, const float *shift, const float *residual, float *y,
+                                         void *workspace, int64_t workspace_bytes, void *stream) {
+    IVX_REQUIRE(p && x_split && weight_split && y, "NULL argument");
+    int rc0 = validate_tc(p, residual != nullptr);
+    if (rc0 != IVX_OK) return rc0;
+    IVX_REQUIRE(p->in_dtype == IVX_F32X2 && p->out_dtype == IVX_F32,
+                "ivx_conv3d_ndhwc_f32x3_tc takes split fp32 activations (IVX_F32X2) and writes fp32");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x_split) | reinterpret_cast<uintptr_t>(y) |
+                 reinterpret_cast<uintptr_t>(weight_split) | reinterpret_cast<uintptr_t>(residual)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    {
+        int perm[3] = {0, 1, 2}, mt = 1;
+        if (use_halo(p, perm, &mt))
+            return launch_conv3d_tc_halo(p, perm, mt, x_split, weight_split, scale, shift, residual, y,
+                                         (cudaStream_t)stream);
+    }
+    return launch_tc<true>(p, x_split, weight_split, scale, shift, residual, y, workspace, workspace_bytes,
+                           (cudaStream_t)stream);
 }

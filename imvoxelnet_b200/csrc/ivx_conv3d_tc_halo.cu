@@ -36,6 +36,14 @@
 // TF32 = true is the same kernel for fp32 tensors with kind::tf32 MMAs: a 128-byte row is 32 channels,
 // so a chunk is 32 input channels and the output is staged as 32-channel fp32 slabs (four per
 // 128-channel tile, which leaves room for one slab set and two plane stages).
+//
+// x3 (fp32-grade results from tf32 MMAs, "3xTF32"): every fp32 operand is the exact sum of a tf32 value
+// `hi` and a remainder `lo`; x*w ~= x_lo*w_hi + x_hi*w_lo + x_hi*w_hi (the dropped x_lo*w_lo term and
+// the rounding of `lo` to tf32 are both ~2^-22 of the product).  The activations come as
+// [..][2*c_in] = (hi | lo) channels (ivx_split_tf32_ndhwc) and the weights as [c_out][2][27*c_in],
+// so the three products are simply three times as many 32-channel chunks of the SAME loop: chunk
+// kc < nc takes (x_lo, w_hi), nc <= kc < 2nc (x_hi, w_lo), the rest (x_hi, w_hi) -- small terms
+// first, into the still small accumulator.  Nothing else in the kernel changes.
 #include <type_traits>
 
 #include "ivx_tc_ptx.cuh"
@@ -63,6 +71,7 @@ struct HaloArgs {
     float post_scale;
     const float *scale, *shift;
     const void *res;
+    int x3;                    // 3xTF32: (hi | lo) activations and weights, three chunk passes
     int debug;                 // IVX_HALO_DEBUG: 1 = epilogue does no work, 2 = no MMA issued (timing decomposition only)
 };
 
@@ -126,7 +135,8 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
-    const int k_chunks = a.c_in / EK;
+    const int nc = a.c_in / EK;                    // 128-byte rows per voxel (of each half, x3)
+    const int k_chunks = a.x3 ? 3 * nc : nc;
     const int n_planes = a.pack2 ? 4 : 3;          // input planes feeding one super-tile
 
     if (warp == 0) {
@@ -140,7 +150,9 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         mbar_wait(smem_u32(a_empty + stage), phase ^ 1);
                         const uint32_t bar = smem_u32(a_full + stage);
                         mbar_expect_tx(bar, (uint32_t)(plane_rows * 128));
-                        tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, kc * EK,
+                        // x3: pass 0 reads the lo half of the channels, passes 1 and 2 the hi half
+                        const int xch = a.x3 ? (kc < nc ? a.c_in + kc * EK : (kc % nc) * EK) : kc * EK;
+                        tma_load_5d(smem_u32(a_base + (size_t)stage * a_bytes), &map_x, bar, xch,
                                     tc.p0 - a.pad[0], tc.q0 - a.pad[1], tc.r0 * a.stride_r - a.pad[2] + dr, tc.b);
                         if (++stage == (uint32_t)a.a_stages) stage = 0, phase ^= 1;
                     }
@@ -159,11 +171,14 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                         const uint32_t bar = smem_u32(b_full + stage);
                         const uint32_t dst = smem_u32(b_base + (size_t)stage * b_bytes);
                         // weights stay packed [c_out][kX][kY][kZ][c_in]; column of tap (dp, dq, dr):
+                        // x3: the row is (hi | lo) x 27 taps x c_in; pass 1 takes the lo half
+                        const int wbase = (a.x3 && kc >= nc && kc < 2 * nc) ? 27 * a.c_in : 0;
+                        const int wch = (a.x3 ? kc % nc : kc) * EK;
                         auto wcol = [&](int dr) {
-                            if (dr < 0 || dr > 2) return 27 * a.c_in;   // beyond the tensor: TMA zero fill
+                            if (dr < 0 || dr > 2) return (a.x3 ? 54 : 27) * a.c_in;   // beyond the tensor: TMA zero fill
                             int k3[3];                                   // tap along the tensor axes X, Y, Z
                             k3[a.axis[0]] = dp, k3[a.axis[1]] = dq, k3[a.axis[2]] = dr;
-                            return ((k3[0] * 3 + k3[1]) * 3 + k3[2]) * a.c_in + kc * EK;
+                            return wbase + ((k3[0] * 3 + k3[1]) * 3 + k3[2]) * a.c_in + wch;
                         };
                         if (a.pack2) {
                             mbar_expect_tx(bar, 2u * 64u * 128u);
@@ -333,7 +348,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
 // Decide whether (and how) the halo kernel takes a layer.  perm[role] = tensor axis (0=X,1=Y,2=Z)
 // playing role P, Q, R.  Returns the fraction of accumulator rows that hold real outputs, or 0.
 double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
-    const int ek = p->in_dtype == IVX_F32 ? 32 : 64;     // channels per 128-byte row: tf32 / bf16
+    const int ek = p->in_dtype == IVX_BF16 ? 64 : 32;    // channels per 128-byte row: bf16 / tf32
     if (p->transposed || p->c_in % ek != 0 || p->c_out % 64 != 0) return 0.0;
     int strided_axis = -1;
     for (int d = 0; d < 3; ++d) {
@@ -379,13 +394,16 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
     const CUtensorMapDataType dt_out = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     HaloArgs a;
     a.c_in = p->c_in, a.c_out = p->c_out;
+    a.x3 = (TF32 && p->in_dtype == IVX_F32X2) ? 1 : 0;
+    const int cin_mem = a.x3 ? 2 * p->c_in : p->c_in;    // channels per voxel in memory
+    const int w_halves = a.x3 ? 2 : 1;
     a.n_tile = p->c_out % 128 == 0 ? 128 : 64;
     a.n_splits = p->c_out / a.n_tile;
     a.mt = mt;
     a.batch = p->batch;
     // element strides of the channels-last tensors along X, Y, Z
-    const long long in_s[3] = {(long long)p->in_dims[1] * p->in_dims[2] * p->c_in,
-                               (long long)p->in_dims[2] * p->c_in, (long long)p->c_in};
+    const long long in_s[3] = {(long long)p->in_dims[1] * p->in_dims[2] * cin_mem,
+                               (long long)p->in_dims[2] * cin_mem, (long long)cin_mem};
     const long long out_s[3] = {(long long)p->out_dims[1] * p->out_dims[2] * p->c_out,
                                 (long long)p->out_dims[2] * p->c_out, (long long)p->c_out};
     for (int r = 0; r < 3; ++r) {
@@ -431,7 +449,7 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
 
     alignas(64) CUtensorMap map_x, map_w, map_y, map_r;
     {
-        const cuuint64_t dims[5] = {(cuuint64_t)p->c_in, (cuuint64_t)p->in_dims[perm[0]],
+        const cuuint64_t dims[5] = {(cuuint64_t)cin_mem, (cuuint64_t)p->in_dims[perm[0]],
                                     (cuuint64_t)p->in_dims[perm[1]], (cuuint64_t)p->in_dims[perm[2]],
                                     (cuuint64_t)p->batch};
         const cuuint64_t st[4] = {(cuuint64_t)in_s[perm[0]] * ES, (cuuint64_t)in_s[perm[1]] * ES,
@@ -442,8 +460,8 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
         if (rc != IVX_OK) return rc;
     }
     {
-        const cuuint64_t dims[2] = {(cuuint64_t)27 * p->c_in, (cuuint64_t)p->c_out};
-        const cuuint64_t st[1] = {(cuuint64_t)27 * p->c_in * ES};
+        const cuuint64_t dims[2] = {(cuuint64_t)27 * w_halves * p->c_in, (cuuint64_t)p->c_out};
+        const cuuint64_t st[1] = {(cuuint64_t)27 * w_halves * p->c_in * ES};
         const cuuint32_t box[2] = {EK, (cuuint32_t)a.n_tile};   // pack2: two such loads fill the 128 rows
         const cuuint32_t es[2] = {1, 1};
         int rc = encode_map_sw128(&map_w, dt_in, 2, const_cast<void *>(weight_bf16), dims, st, box, es, "weights (halo)");
@@ -477,7 +495,7 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
 int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
                           const void *weight, const float *scale, const float *shift,
                           const void *residual, void *y, cudaStream_t stream) {
-    if (p->in_dtype == IVX_F32)
+    if (p->in_dtype != IVX_BF16)
         return launch_halo<true>(p, perm, mt, x, weight, scale, shift, residual, y, stream);
     return launch_halo<false>(p, perm, mt, x, weight, scale, shift, residual, y, stream);
 }

@@ -16,22 +16,26 @@ import torch
 from torch import nn
 
 from .conv import FusedConv, from_ndhwc, to_ndhwc, upsample2x_trilinear
+from .conv import fp32x3 as conv_fp32x3
 from .conv import tf32 as conv_tf32
 from .registry import NECKS, register
 
 __all__ = ["FastIndoorImVoxelNeck", "ImVoxelNeck", "KittiImVoxelNeck", "NuScenesImVoxelNeck"]
 
-PRECISIONS = ("fp32", "tf32", "bf16")
+PRECISIONS = ("fp32", "fp32_simt", "tf32", "bf16")
 
 
 class _NeckBase(nn.Module):
-    #: "fp32": fp32 activations, CUDA-core kernels, matches the reference to 1e-5.
+    #: "fp32": fp32 activations, matches the reference to 1e-5: layers with c_in % 32 == 0 and
+    #:         c_out % 64 == 0 run on the tensor cores as three tf32 products (3xTF32), the rest on
+    #:         the CUDA-core kernel.
+    #: "fp32_simt": fp32 activations, every layer on the CUDA-core kernel (1e-5; the slow cross-check).
     #: "tf32": fp32 activations, tf32 tensor-core math (what cuDNN does for fp32 by default; 1e-3).
     #: "bf16": bf16 activations, tensor-core kernels where available (1e-2).
     precision = "fp32"
 
     def __call__(self, *args, **kwargs):
-        with conv_tf32(self.precision == "tf32"):
+        with conv_tf32(self.precision == "tf32"), conv_fp32x3(self.precision != "fp32_simt"):
             return super().__call__(*args, **kwargs)
 
     def init_weights(self):

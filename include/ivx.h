@@ -46,7 +46,12 @@ typedef enum ivx_status {
 } ivx_status;
 
 /* element type of a volume written by the library */
-typedef enum ivx_dtype { IVX_F32 = 0, IVX_BF16 = 1, IVX_U8 = 2 /* masks only */ } ivx_dtype;
+typedef enum ivx_dtype {
+    IVX_F32 = 0,
+    IVX_BF16 = 1,
+    IVX_U8 = 2,   /* masks only */
+    IVX_F32X2 = 3 /* fp32 split into two tf32 values, channels (hi | lo): ivx_split_tf32_ndhwc */
+} ivx_dtype;
 
 /* what ivx_backproject_scenes writes */
 typedef enum ivx_reduce {
@@ -371,6 +376,35 @@ IVX_API int ivx_conv3d_ndhwc_bf16_tc(const ivx_conv3d_params *params, const void
 IVX_API int ivx_conv3d_ndhwc_tf32_tc(const ivx_conv3d_params *params, const float *x, const float *weight,
                                      const float *scale, const float *shift, const float *residual, float *y,
                                      void *workspace, int64_t workspace_bytes, void *stream);
+
+/*
+ * ivx_conv3d_ndhwc_f32x3_tc -- the same layer with fp32-grade results on the
+ * tensor cores ("3xTF32"): what the reference computes, an fp32 nn.Conv3d
+ * (necks/imvoxelnet.py:116-120 is not autocast and no config sets fp16; the
+ * pinned torch 1.6 has no TF32), within 1e-5.  Every fp32 value is the exact
+ * sum of a tf32 number hi and a remainder lo; the kernel accumulates
+ * x_lo*w_hi + x_hi*w_lo + x_hi*w_hi in fp32 (TMEM) as three passes of the tf32
+ * kernel above -- the dropped x_lo*w_lo and the rounding of lo are each about
+ * 2^-22 of a product.
+ *   params         in_dtype = IVX_F32X2, out_dtype = IVX_F32; c_in is the layer's
+ *                  channel count (c_in % 32 == 0, c_out % 64 == 0)
+ *   x_split        [batch][in_dims][2*c_in] fp32, written by ivx_split_tf32_ndhwc
+ *   weight_split   fp32 [c_out][2][kX*kY*kZ][c_in]: the tf32_tc layout with every
+ *                  row holding its hi taps, then its lo taps; transposed layers
+ *                  [kX*kY*kZ][c_out][2][c_in].  hi = w rounded to tf32, lo = w - hi.
+ *   residual, y    plain fp32 [batch][out_dims][c_out]
+ *   workspace      as for ivx_conv3d_ndhwc_bf16_tc (ivx_conv3d_tc_workspace_bytes
+ *                  with these params)
+ *
+ * ivx_split_tf32_ndhwc -- x [rows][C] fp32 -> y [rows][2*C]: hi = rna_tf32(x),
+ * lo = rna_tf32(x - hi); C % 4 == 0.  One coalesced pass (4 B read, 8 B written
+ * per element).
+ */
+IVX_API int ivx_conv3d_ndhwc_f32x3_tc(const ivx_conv3d_params *params, const float *x_split,
+                                      const float *weight_split, const float *scale, const float *shift,
+                                      const float *residual, float *y, void *workspace,
+                                      int64_t workspace_bytes, void *stream);
+IVX_API int ivx_split_tf32_ndhwc(const float *x, float *y, int64_t rows, int n_channels, void *stream);
 
 /*
  * ivx_upsample2x_trilinear_ndhwc -- F.interpolate(x, scale_factor=2,

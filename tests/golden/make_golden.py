@@ -149,9 +149,21 @@ def main():
     out["P_total_angles"] = det.ImVoxelNet._compute_projection(sc.img_meta, 4, angles[:1]).numpy()
     np.savez(os.path.join(HERE, "host_setup.npz"), **out)
 
-    # 6. full-size configurations: digests of the reference outputs
+    make_digests(FULLSIZE)
+
+
+FULLSIZE = ("sunrgbd_fast", "kitti", "scannet_fast", "nuscenes", "total_sunrgbd", "nuscenes_refgrid")
+
+
+def make_digests(names):
+    """6. full-size configurations: digests of the reference outputs.  Entries of configurations not
+    in `names` are kept as they are in the file (`--digests NAME ...` adds one without redoing all)."""
+    path = os.path.join(HERE, "fullsize_digests.npz")
     dig = {}
-    for name in ("sunrgbd_fast", "kitti", "scannet_fast", "nuscenes", "total_sunrgbd"):
+    if os.path.isfile(path):
+        with np.load(path) as old:
+            dig = {k: old[k] for k in old.files}
+    for name in names:
         sc = scenes.build(name)
         full, feats, pts, P = scene_inputs(sc, seed=100)
         x, y, valid = reference_indices(feats, pts, P)
@@ -170,10 +182,12 @@ def main():
         dig[f"{name}_sample_val"] = v.reshape(-1)[rs]
         dig[f"{name}_features_sha"] = sha(full.numpy())
         print(name, "n_valid", dig[f"{name}_n_valid"], "covered", dig[f"{name}_covered"])
-    np.savez(os.path.join(HERE, "fullsize_digests.npz"), **dig)
+    np.savez(path, **dig)
 
 
-if __name__ == "__main__" and not {"--necks", "--heads"} & set(sys.argv):
+if __name__ == "__main__" and "--digests" in sys.argv:
+    make_digests(sys.argv[sys.argv.index("--digests") + 1:])
+elif __name__ == "__main__" and not {"--necks", "--heads"} & set(sys.argv):
     main()
 
 

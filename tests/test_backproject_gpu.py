@@ -21,7 +21,7 @@ from tests.util import assert_volume_close, load_golden, sha
 pytestmark = pytest.mark.gpu
 
 SMALL = ["bp_ring5", "bp_kitti_small", "bp_nus6", "bp_ties"]
-FULL = ["sunrgbd_fast", "kitti", "scannet_fast", "nuscenes", "total_sunrgbd"]
+FULL = ["sunrgbd_fast", "kitti", "scannet_fast", "nuscenes", "total_sunrgbd", "nuscenes_refgrid"]
 DEV = "cuda:0"
 
 

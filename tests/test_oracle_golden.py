@@ -119,7 +119,7 @@ def test_host_setup_golden(golden_dir):
     assert np.array_equal(P, g["P_total_angles"])
 
 
-@pytest.mark.parametrize("name", ["sunrgbd_fast", "kitti", "scannet_fast", "nuscenes", "total_sunrgbd"])
+@pytest.mark.parametrize("name", ["sunrgbd_fast", "kitti", "scannet_fast", "nuscenes", "total_sunrgbd", "nuscenes_refgrid"])
 def test_fullsize_digests(golden_dir, name):
     """BASELINE.json's full-size configurations against digests of the
     reference's outputs on the same seeded inputs."""

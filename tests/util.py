@@ -29,3 +29,12 @@ def assert_volume_close(got, ref, rel=VOLUME_RTOL, atol=VOLUME_ATOL):
     err = np.abs(got - ref)
     worst = float(err.max()) if err.size else 0.0
     assert worst <= rel * (scale or 1.0) + atol, f"max err {worst:.3e} (scale {scale:.3e})"
+
+
+def rel_l2(got, ref):
+    """||got - ref||_2 / ||ref||_2 (float64) of two arrays or torch tensors."""
+    if hasattr(got, "detach"):
+        d = (got.detach().double() - ref.detach().double()).norm().item()
+        return d / max(ref.detach().double().norm().item(), 1e-300)
+    got, ref = np.asarray(got, dtype=np.float64), np.asarray(ref, dtype=np.float64)
+    return float(np.linalg.norm(got - ref) / max(np.linalg.norm(ref), 1e-300))

@@ -115,7 +115,8 @@ def main():
             rows = y.numel() // y.shape[-1] if not self.transposed else xx.numel() // xx.shape[-1]
             fl = 2.0 * rows * self.conv.in_channels * self.conv.out_channels * taps
             desc = "%-28s -> %-28s k%s s%s %s%s" % (tuple(xx.shape), tuple(y.shape), ks[0], self.conv.stride,
-                                                  "tc" if self.tc_eligible(xx, y.dtype) else "simt",
+                                                  "tc" if self.tc_eligible(xx, y.dtype) else ("tf32" if self.tf32_eligible(xx, y.dtype) else
+                                                                                                 ("3xtf32" if self.x3_eligible(xx, y.dtype) else "simt")),
                                                   " +res" if k.get("residual") is not None else "")
             note(counter[0], desc, e0.elapsed_time(e1), fl)
             counter[0] += 1
