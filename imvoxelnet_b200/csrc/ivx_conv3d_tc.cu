@@ -72,6 +72,7 @@ struct TcArgs {
     // 3xTF32 (fp32-grade results, see ivx_conv3d_tc_halo.cu): activations are (hi | lo) channels, weight
     // rows (hi | lo) x taps x c_in; the k-steps run three passes (x_lo w_hi, x_hi w_lo, x_hi w_hi)
     int x3;
+    int drain_steps;            // x3: k-steps (of 4 MMAs) per accumulation period (x3_accumulate_periods)
 };
 
 struct TileCoord {
@@ -154,7 +155,7 @@ __device__ __forceinline__ uint4 epilogue4(const uint32_t *v, uint32_t ss_addr, 
 // TF32 = false: bf16 storage, kind::f16 MMAs, 64 channels per 128-byte k-step and per output slab.
 // TF32 = true : fp32 storage, kind::tf32 MMAs (the TMA rounds the operands to tf32), 32 channels per
 //               k-step; a 64-channel output chunk is two 32-channel slabs, one per epilogue warp half.
-template <bool TF32>
+template <bool TF32, bool X3 = false>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                  const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_r,
@@ -242,26 +243,41 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const uint32_t idesc = TF32 ? umma_idesc_tf32(a.n_tile) : umma_idesc(a.n_tile);
             uint32_t stage = 0, phase = 0, acc = 0, acc_phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
-                mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);  // epilogue drained this accumulator
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t d_tmem = tmem_base + acc * acc_stride;
+                if (!X3) {
+                    mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);  // epilogue drained this accumulator
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                uint32_t d_tmem = tmem_base + acc * acc_stride;
                 const int k_lo = (int)(t % a.k_splits) * a.steps_per_split;
                 const int my_steps = min(k_steps, k_lo + a.steps_per_split) - k_lo;
+                int in_period = 0;                 // x3: k-steps issued into the current accumulation period
                 for (int ks = 0; ks < my_steps; ++ks) {
+                    if (X3 && in_period == 0) {    // a new period starts in the other accumulator
+                        mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        d_tmem = tmem_base + acc * acc_stride;
+                    }
                     mbar_wait(smem_u32(full_bar + stage), phase);
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                     const uint32_t sa = smem_u32(stage_base + (size_t)stage * stage_bytes);
                     const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TC_A_BYTES);
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {   // +32 bytes per MMA (K = 16 bf16 / 8 tf32) inside the swizzle row
-                        if (TF32) umma_tf32(d_tmem, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
+                        if (TF32) umma_tf32(d_tmem, da + 2 * k, db + 2 * k, idesc, ((X3 ? in_period : ks) | k) != 0);
                         else umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (ks | k) != 0);
                     }
                     umma_commit(smem_u32(empty_bar + stage));  // frees the smem stage when the MMAs retire
                     if (++stage == (uint32_t)a.stages) stage = 0, phase ^= 1;
+                    if (X3 && (++in_period == a.drain_steps || ks + 1 == my_steps)) {
+                        umma_commit(smem_u32(acc_full + acc));  // period complete
+                        if (++acc == 2) acc = 0, acc_phase ^= 1;
+                        in_period = 0;
+                    }
                 }
-                umma_commit(smem_u32(acc_full + acc));  // accumulator complete
-                if (++acc == 2) acc = 0, acc_phase ^= 1;
+                if (!X3) {
+                    umma_commit(smem_u32(acc_full + acc));  // accumulator complete
+                    if (++acc == 2) acc = 0, acc_phase ^= 1;
+                }
             }
         }
     } else {
@@ -304,7 +320,18 @@ conv3d_tc_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constan
             const int ox = tc.x0 + ix, oy = tc.y0 + iy, oz = tc.z0 + iz;
             const bool row_ok = row < box_rows && ox < a.out_dims[0] && oy < a.out_dims[1] && oz < a.out_dims[2];
             const long long ovox = (((long long)tc.b * a.out_dims[0] + ox) * a.out_dims[1] + oy) * a.out_dims[2] + oz;
-            mbar_wait(smem_u32(acc_full + acc), acc_phase);
+            if (X3) {
+                // sum the accumulation periods of this tile in registers and put the sum back into the last
+                // accumulator: this warp's 32 lanes x its 32 columns of every 64-column chunk -- exactly the
+                // cells it reads below, so no other warp has to wait for the write-back
+                const int k_lo = (int)(t % a.k_splits) * a.steps_per_split;
+                const int my_steps = min(k_steps, k_lo + a.steps_per_split) - k_lo;
+                x3_accumulate_periods(tmem_base, (uint32_t)acc_stride, ((uint32_t)(q * 32) << 16) + half * 32,
+                                      a.n_tile / 64, 64u, (my_steps + a.drain_steps - 1) / a.drain_steps, acc_full,
+                                      acc_empty, acc, acc_phase, lane);
+            } else {
+                mbar_wait(smem_u32(acc_full + acc), acc_phase);
+            }
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             float *ws_row = nullptr;
             if (a.k_splits > 1) {
@@ -587,6 +614,11 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     // fp32 partials that go through the L2 workspace (needs a workspace; the caller may not have
     // one -> k_splits reset to 1 later).
     a.x3 = p->in_dtype == IVX_F32X2 ? 1 : 0;
+    {
+        const char *e = getenv("IVX_X3_DRAIN_STEPS");    // experiments: a huge value = one period per tile
+        a.drain_steps = e ? atoi(e) : 16;
+        if (a.drain_steps < 1) a.drain_steps = 1;
+    }
     const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / (p->in_dtype == IVX_BF16 ? 64 : 32)) *
                         (a.x3 ? 3 : 1);
     a.k_splits = 1;
@@ -621,7 +653,7 @@ extern "C" int64_t ivx_conv3d_tc_workspace_bytes(const ivx_conv3d_params *p) {
 }
 
 // Launch of the per-tap kernel in either storage type (the bf16 entry point tries the halo kernel first).
-template <bool TF32>
+template <bool TF32, bool X3 = false>
 static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weight, const float *scale,
                      const float *shift, const void *residual, void *y, void *workspace, int64_t workspace_bytes,
                      cudaStream_t stream, const int64_t *y_strides = nullptr) {
@@ -736,12 +768,12 @@ static int launch_tc(const ivx_conv3d_params *p, const void *x, const void *weig
         }
     }
 
-    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_kernel<TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_kernel<TF32, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem),
                         "cudaFuncSetAttribute");
     if (rc != IVX_OK) return rc;
     const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
-    conv3d_tc_kernel<TF32><<<grid, TC_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
+    conv3d_tc_kernel<TF32, X3><<<grid, TC_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
     IVX_CHECK_LAUNCH("conv3d_tc launch");
     return IVX_OK;
 }
@@ -817,6 +849,6 @@ extern "C" int ivx_conv3d_ndhwc_f32x3_tc(const ivx_conv3d_params *p, const float
             return launch_conv3d_tc_halo(p, perm, mt, x_split, weight_split, scale, shift, residual, y,
                                          (cudaStream_t)stream);
     }
-    return launch_tc<true>(p, x_split, weight_split, scale, shift, residual, y, workspace, workspace_bytes,
-                           (cudaStream_t)stream);
+    return launch_tc<true, true>(p, x_split, weight_split, scale, shift, residual, y, workspace, workspace_bytes,
+                                 (cudaStream_t)stream);
 }

@@ -43,7 +43,11 @@
 // [..][2*c_in] = (hi | lo) channels (ivx_split_tf32_ndhwc) and the weights as [c_out][2][27*c_in],
 // so the three products are simply three times as many 32-channel chunks of the SAME loop: chunk
 // kc < nc takes (x_lo, w_hi), nc <= kc < 2nc (x_hi, w_lo), the rest (x_hi, w_hi) -- small terms
-// first, into the still small accumulator.  Nothing else in the kernel changes.
+// first.  The tensor core's truncating accumulate would still leave an error linear in K, so the x3
+// instantiation hands an accumulator over after every `drain_groups` (chunk, plane) groups of 36 MMAs
+// and eight epilogue warps (warps 7..10 help: each warp takes half of the columns of its TMEM lane
+// quarter) sum the periods in registers (x3_accumulate_periods, ivx_tc_ptx.cuh); the sum is written
+// back to TMEM and the usual epilogue (warps 3..6) runs on it.
 #include <type_traits>
 
 #include "ivx_tc_ptx.cuh"
@@ -51,6 +55,7 @@
 namespace ivx {
 
 constexpr int HL_THREADS = 224;
+constexpr int HL_THREADS_X3 = 352;   // + 4 warps that help summing the accumulation periods
 constexpr int HL_P = 8, HL_PPAD = 10, HL_QT = 16;  // outputs per group, box rows along P (8 + halo), groups per tile
 
 struct HaloArgs {
@@ -72,6 +77,7 @@ struct HaloArgs {
     const float *scale, *shift;
     const void *res;
     int x3;                    // 3xTF32: (hi | lo) activations and weights, three chunk passes
+    int drain_groups;          // x3: (chunk, plane) groups of 36 MMAs per accumulation period
     int debug;                 // IVX_HALO_DEBUG: 1 = epilogue does no work, 2 = no MMA issued (timing decomposition only)
 };
 
@@ -92,8 +98,8 @@ __device__ __forceinline__ HaloTile decode_halo_tile(const HaloArgs &a, long lon
     return c;
 }
 
-template <bool TF32>
-__global__ void __launch_bounds__(HL_THREADS, 1)
+template <bool TF32, bool X3>
+__global__ void __launch_bounds__(X3 ? HL_THREADS_X3 : HL_THREADS, 1)
 conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_w,
                       const __grid_constant__ CUtensorMap map_y, const __grid_constant__ CUtensorMap map_r,
                       const __grid_constant__ HaloArgs a) {
@@ -122,7 +128,7 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     if (threadIdx.x == 0) {
         for (int s = 0; s < a.a_stages; ++s) mbar_init(smem_u32(a_full + s), 1), mbar_init(smem_u32(a_empty + s), 1);
         for (int s = 0; s < a.b_stages; ++s) mbar_init(smem_u32(b_full + s), 1), mbar_init(smem_u32(b_empty + s), 1);
-        for (int i = 0; i < 2; ++i) mbar_init(smem_u32(acc_full + i), 1), mbar_init(smem_u32(acc_empty + i), 4);
+        for (int i = 0; i < 2; ++i) mbar_init(smem_u32(acc_full + i), 1), mbar_init(smem_u32(acc_empty + i), X3 ? 8 : 4);
         for (int i = 0; i < 2; ++i) mbar_init(smem_u32(res_bar + i), 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("prefetch.tensormap [%0];" ::"l"(&map_x) : "memory");
@@ -138,6 +144,8 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
     const int nc = a.c_in / EK;                    // 128-byte rows per voxel (of each half, x3)
     const int k_chunks = a.x3 ? 3 * nc : nc;
     const int n_planes = a.pack2 ? 4 : 3;          // input planes feeding one super-tile
+    const int n_groups = k_chunks * n_planes;      // (chunk, plane) groups of 36 MMAs per tile
+    const int n_periods = X3 ? (n_groups + a.drain_groups - 1) / a.drain_groups : 1;
 
     if (warp == 0) {
         // -------- activation planes: (chunk, dR) -> one box of 10 x (16*MT + 2) voxels --------
@@ -198,12 +206,21 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
             const uint32_t idesc = TF32 ? umma_idesc_tf32(128 * a.mt) : umma_idesc(128 * a.mt);   // M = 128 channel lanes, N = voxels
             uint32_t sa = 0, pa = 0, sb = 0, pb = 0, acc = 0, acc_phase = 0;
             for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
-                mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t d_tmem = tmem_base + acc * acc_cols;
+                if (!X3) {
+                    mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                }
+                uint32_t d_tmem = tmem_base + acc * acc_cols;
                 bool first = true;
+                int gi = 0;
                 for (int kc = 0; kc < k_chunks; ++kc)
                     for (int dr = 0; dr < n_planes; ++dr) {
+                        if (X3 && gi % a.drain_groups == 0) {   // a new accumulation period, in the other accumulator
+                            mbar_wait(smem_u32(acc_empty + acc), acc_phase ^ 1);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            d_tmem = tmem_base + acc * acc_cols;
+                            first = true;
+                        }
                         mbar_wait(smem_u32(a_full + sa), pa);
                         const uint32_t plane = smem_u32(a_base + (size_t)sa * a_bytes);
                         for (int dq = 0; dq < 3; ++dq)
@@ -228,10 +245,31 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                             }
                         umma_commit(smem_u32(a_empty + sa));
                         if (++sa == (uint32_t)a.a_stages) sa = 0, pa ^= 1;
+                        ++gi;
+                        if (X3 && (gi % a.drain_groups == 0 || gi == n_groups)) {
+                            umma_commit(smem_u32(acc_full + acc));
+                            if (++acc == 2) acc = 0, acc_phase ^= 1;
+                        }
                     }
-                umma_commit(smem_u32(acc_full + acc));
-                if (++acc == 2) acc = 0, acc_phase ^= 1;
+                if (!X3) {
+                    umma_commit(smem_u32(acc_full + acc));
+                    if (++acc == 2) acc = 0, acc_phase ^= 1;
+                }
             }
+        }
+    } else if (X3 && warp >= 7) {
+        // ---------------- x3 helpers (warps 7..10): upper half of the columns of each period ----------------
+        const int q4 = warp & 3;
+        const uint32_t half_cols = (uint32_t)acc_cols >> 1;
+        uint32_t acc = 0, acc_phase = 0;
+        for (long long t = blockIdx.x; t < a.n_tiles; t += gridDim.x) {
+            x3_accumulate_periods(tmem_base, (uint32_t)acc_cols, ((uint32_t)(q4 * 32) << 16) + half_cols,
+                                  (int)(half_cols >> 5), 32u, n_periods, acc_full, acc_empty, acc, acc_phase, lane);
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            asm volatile("bar.sync 2, 256;" ::: "memory");     // the sum is in TMEM for warps 3..6
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(acc_empty + acc));
+            if (++acc == 2) acc = 0, acc_phase ^= 1;
         }
     } else {
         // ------------------------------ epilogue (warps 3..6) ------------------------------
@@ -286,7 +324,14 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
                 if (res_ahead)
                     for (int mt = 1; mt < a.mt; ++mt) load_residual(tc, mt, (set + mt) % slab_sets, slab_sets - 1 - mt);
             }
-            mbar_wait(smem_u32(acc_full + acc), acc_phase);
+            if (X3) {   // sum the accumulation periods (lower half of the columns; warps 7..10 take the upper)
+                x3_accumulate_periods(tmem_base, (uint32_t)acc_cols, (uint32_t)(q4 * 32) << 16, acc_cols >> 6, 32u,
+                                      n_periods, acc_full, acc_empty, acc, acc_phase, lane);
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                asm volatile("bar.sync 2, 256;" ::: "memory");
+            } else {
+                mbar_wait(smem_u32(acc_full + acc), acc_phase);
+            }
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             for (int mt = 0; mt < (a.debug == 1 ? 0 : a.mt); ++mt) {
                 if (has_res) {
@@ -385,7 +430,7 @@ double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
     return (double)p->out_dims[perm[0]] * p->out_dims[perm[1]] / (double)(tp * HL_P * tq * HL_QT * *mt_out);
 }
 
-template <bool TF32>
+template <bool TF32, bool X3 = false>
 static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
                        const void *weight_bf16, const float *scale, const float *shift,
                        const void *residual, void *y, cudaStream_t stream) {
@@ -394,7 +439,12 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
     const CUtensorMapDataType dt_out = TF32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
     HaloArgs a;
     a.c_in = p->c_in, a.c_out = p->c_out;
-    a.x3 = (TF32 && p->in_dtype == IVX_F32X2) ? 1 : 0;
+    a.x3 = X3 ? 1 : 0;
+    {
+        const char *e = getenv("IVX_X3_DRAIN_GROUPS");   // experiments: a huge value = one period per tile
+        a.drain_groups = e ? atoi(e) : 4;
+        if (a.drain_groups < 1) a.drain_groups = 1;
+    }
     const int cin_mem = a.x3 ? 2 * p->c_in : p->c_in;    // channels per voxel in memory
     const int w_halves = a.x3 ? 2 : 1;
     a.n_tile = p->c_out % 128 == 0 ? 128 : 64;
@@ -482,12 +532,12 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
             if (rc != IVX_OK) return rc;
         }
     }
-    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_halo_kernel<TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    int rc = check_cuda(cudaFuncSetAttribute(conv3d_tc_halo_kernel<TF32, X3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              (int)smem),
                         "cudaFuncSetAttribute");
     if (rc != IVX_OK) return rc;
     const unsigned grid = (unsigned)(a.n_tiles < kNumSMs ? a.n_tiles : kNumSMs);
-    conv3d_tc_halo_kernel<TF32><<<grid, HL_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
+    conv3d_tc_halo_kernel<TF32, X3><<<grid, X3 ? HL_THREADS_X3 : HL_THREADS, smem, stream>>>(map_x, map_w, map_y, map_r, a);
     IVX_CHECK_LAUNCH("conv3d_tc_halo launch");
     return IVX_OK;
 }
@@ -495,6 +545,8 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
 int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
                           const void *weight, const float *scale, const float *shift,
                           const void *residual, void *y, cudaStream_t stream) {
+    if (p->in_dtype == IVX_F32X2)
+        return launch_halo<true, true>(p, perm, mt, x, weight, scale, shift, residual, y, stream);
     if (p->in_dtype != IVX_BF16)
         return launch_halo<true>(p, perm, mt, x, weight, scale, shift, residual, y, stream);
     return launch_halo<false>(p, perm, mt, x, weight, scale, shift, residual, y, stream);

@@ -128,6 +128,71 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         : "memory");
 }
 
+// registers -> TMEM: 32 lanes x 32 consecutive columns (the inverse of tmem_ld32)
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+          "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+          "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+        : "memory");
+}
+
+// 3xTF32 accumulation (fp32-grade layers).  The tensor core adds each MMA's products into the TMEM
+// accumulator with truncation, so thousands of MMAs into ONE accumulator leave an error that grows
+// linearly with K (measured: 1.6e-6 of max|out| at K = 1728, 1.1e-5 at K = 13 824).  The x3 kernels
+// therefore give an accumulator only a short run of MMAs (a "period"), alternate between the two
+// TMEM accumulators, and the epilogue warps add every finished period into fp32 registers
+// (round-to-nearest) -- `master`, 128 values per thread, this warp's 32 TMEM lanes x up to 128 of the
+// columns in 32-column chunks `stride` apart.  After the last period the sum is written back over the
+// accumulator it came from and the ordinary fused epilogue runs on it.
+//   n_chunks        32-column chunks of this warp (<= 4); chunk i starts at column col0 + i * stride
+//   acc, acc_phase  accumulator / mbarrier parity bookkeeping, shared with the rest of the epilogue:
+//                   on return `acc` is the buffer that holds the sum and is NOT yet released
+__device__ __forceinline__ void x3_accumulate_periods(uint32_t tmem_base, uint32_t acc_cols_stride, uint32_t lane_col0,
+                                                      int n_chunks, uint32_t stride, int n_periods,
+                                                      uint64_t *acc_full, uint64_t *acc_empty, uint32_t &acc,
+                                                      uint32_t &acc_phase, int lane) {
+    float master[128];
+#pragma unroll
+    for (int i = 0; i < 128; ++i) master[i] = 0.f;
+    for (int per = 0; per < n_periods; ++per) {
+        mbar_wait(smem_u32(acc_full + acc), acc_phase);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t base = tmem_base + acc * acc_cols_stride + lane_col0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            if (i < n_chunks) {
+                uint32_t v[32];
+                tmem_ld32(base + (uint32_t)i * stride, v);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int j = 0; j < 32; ++j) master[i * 32 + j] += __uint_as_float(v[j]);
+            }
+        }
+        if (per + 1 < n_periods) {   // hand the accumulator back; the last one is kept for the epilogue
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(acc_empty + acc));
+            if (++acc == 2) acc = 0, acc_phase ^= 1;
+        }
+    }
+    const uint32_t base = tmem_base + acc * acc_cols_stride + lane_col0;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        if (i < n_chunks) {
+            uint32_t v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(master[i * 32 + j]);
+            tmem_st32(base + (uint32_t)i * stride, v);
+        }
+    }
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
 // bf16 x bf16 -> fp32, both operands K-major, M = 128
 __device__ __forceinline__ uint32_t umma_idesc(int n) {
     return (1u << 4)                      // accumulator format F32
