@@ -9,9 +9,11 @@ then the configuration's 3D neck -- over one batch of synthetic scenes of the
 named configuration.  Default workload: ``imvoxelnet_kitti`` -- 1280x384
 monocular, 216x248x12 voxels, 64 channels, batch 8 (BASELINE.json configs[1]).
 For N > 1 every rank processes its own batch of scenes (plain data-parallel,
-no collective on the data path: "scaling": "weak"); ``--workload
-scannet_fast`` instead shards the 50 views of each scene over the ranks and
-all-reduces the partial sums/counts over NCCL.
+no collective on the data path: "scaling": "weak").  The same line carries, under
+``view_sharded``, the strong-scaling figures of the multi-view configurations
+(50-view ScanNet, 6-camera nuScenes) whose VIEWS are sharded over the N ranks
+with the reduction fused into the finalize kernel; ``--workload scannet_fast``
+with N > 1 makes that mode the headline of the line instead.
 
 Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every key.
 """
@@ -148,10 +150,35 @@ def randomize_norms(module, seed=0):
 # --------------------------------------------------------------------------
 # the reference arm: the reference's CPU path (torch port), all host threads
 # --------------------------------------------------------------------------
+def reference_modules():
+    """(scene_volume, neck classes, kind, description) of the CPU arm: the UNMODIFIED reference files
+    (mmdet3d/models/detectors/imvoxelnet.py, necks/imvoxelnet.py, imported by oracle/ref_loader.py) when a
+    copy of the reference tree is on this machine, else the op-for-op port pinned to them."""
+    from oracle import ref_loader, torch_necks, torch_port
+    for root in (os.environ.get("IVX_REFERENCE_ROOT"), "/root/reference", os.path.join(ROOT, "baseline", "_ref")):
+        if root and os.path.isfile(os.path.join(root, "mmdet3d/models/detectors/imvoxelnet.py")):
+            ref_loader.REFERENCE_ROOT = root
+            det, nk = ref_loader.load()
+
+            def scene_volume(features, points, projection):   # detectors/imvoxelnet.py:69-74, verbatim statements
+                volume, valid = det.backproject(features, points, projection)
+                volume = volume.sum(dim=0)
+                valid = valid.sum(dim=0)
+                volume = volume / valid
+                valid = valid > 0
+                volume[:, ~valid[0]] = .0
+                return volume, valid
+
+            return scene_volume, (lambda name: getattr(nk, name)), "reference", \
+                f"the unmodified reference files under {root} (oracle/ref_loader.py)"
+    return torch_port.scene_volume, (lambda name: torch_necks.NECKS[name]), "port", \
+        "torch-CPU port of the reference (oracle/torch_port.py, oracle/torch_necks.py; no reference tree here)"
+
+
 def cpu_reference_time(sc, P, origin, workload, repeats, warmup, with_neck, seed=0):
-    """Seconds per scene of the reference's torch-CPU path: backproject + view
-    mean (oracle/torch_port.py) and, if asked, the neck (oracle/torch_necks.py)."""
-    from oracle import torch_necks, torch_port
+    """Seconds per scene of the reference's CPU path: backproject + view mean and, if asked,
+    the neck, on all host threads.  Returns (times, kind, description)."""
+    scene_volume, neck_class, kind, what = reference_modules()
     torch.set_num_threads(os.cpu_count() or 1)
     full = scenes.random_features(sc, seed=seed, channels_last=False)
     h, w = sc.feat_hw
@@ -161,18 +188,18 @@ def cpu_reference_time(sc, P, origin, workload, repeats, warmup, with_neck, seed
     if with_neck and NECKS[workload] is not None:
         name, kw, _ = NECKS[workload]
         torch.manual_seed(0)
-        neck = randomize_norms(torch_necks.NECKS[name](**kw).eval())
+        neck = randomize_norms(neck_class(name)(**kw).eval())
     times = []
     with torch.no_grad():
         for i in range(warmup + repeats):
             t0 = time.perf_counter()
-            vol, _ = torch_port.scene_volume(feats, pts, P)
+            vol, _ = scene_volume(feats, pts, P)
             if neck is not None:
                 neck(vol[None])
             dt = time.perf_counter() - t0
             if i >= warmup:
                 times.append(dt)
-    return times
+    return times, kind, what
 
 
 def run_reference(args):
@@ -182,8 +209,9 @@ def run_reference(args):
     sc, batch, P, origin = scene_setup(args.workload)
     with_neck = not args.no_neck and NECKS[args.workload] is not None
     # a step = ONE scene of the batch (bounded sample of the workload)
-    times = cpu_reference_time(sc, P, origin, args.workload, repeats=args.steps,
-                               warmup=1 if with_neck else max(1, min(args.warmup, 2)), with_neck=with_neck)
+    times, kind, what = cpu_reference_time(sc, P, origin, args.workload, repeats=args.steps,
+                                           warmup=1 if with_neck else max(1, min(args.warmup, 2)),
+                                           with_neck=with_neck)
     t = sum(times) / len(times)
     value = sc.voxel_views / t
     cores = os.cpu_count() or 1
@@ -196,10 +224,9 @@ def run_reference(args):
         "config": config_of(sc, batch, 1, {"stages": stages,
                                            "note": "one scene per step (bounded sample of the batch)"}),
         "scenes_per_s": 1.0 / t,
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": f"{args.steps} x 1 scene of {sc.name}: torch {torch.__version__} CPU "
-                                   f"ops of the reference's {' + '.join(stages)} (oracle/torch_port.py, "
-                                   f"oracle/torch_necks.py), {cores} threads"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{args.steps} x 1 scene of {sc.name}: {' + '.join(stages)} by {what}, "
+                                   f"torch {torch.__version__} CPU, {cores} threads"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -247,6 +274,207 @@ def timed_graph(fn, steps, barrier, repeats=5):
     return statistics.median(totals), graph
 
 
+def pin_to_gpu_cpus(index):
+    """Bind this process (and the pinned buffers it touches first) to the CPUs NVML reports as
+    nearest to GPU `index`.  Returns the number of CPUs in the set, or None when unavailable."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return len(cpus)
+    except Exception:
+        pass
+    return None
+
+
+def tensor_peak(peaks, timed_region_ms):
+    """Measured bf16 tensor peak to compare with: the burst figure for a timed region shorter than
+    about a second (it never reaches the power-capped steady state the sustained figure was taken
+    in), the sustained one from 2 s on."""
+    burst = peaks["bf16_tflops"]
+    sustained = peaks.get("bf16_tflops_sustained", burst)
+    if timed_region_ms >= 2000.0:
+        return sustained, f"sustained (timed region {timed_region_ms / 1e3:.2f} s)"
+    return burst, f"burst (timed region {timed_region_ms / 1e3:.2f} s < 2 s)"
+
+
+def _event_time(fn, reps, warm=1):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def gpu_reference(sc, batch, P, origin, workload, dev):
+    """Same-box bar, a reported baseline only: the reference's own op sequence run by stock PyTorch on
+    this GPU.  Back-projection: the reference's ATen ops (bmm, round, per-view boolean-mask gather /
+    scatter, sum / count; detectors/imvoxelnet.py:145-160, :70-74) per scene on NCHW maps, eager, fp32.
+    Neck: the reference module structure through cuDNN with TF32 (torch's default for fp32
+    convolutions on this hardware) and in bf16 channels_last_3d.  ms per batch."""
+    scene_volume, neck_class, kind, what = reference_modules()
+    h, w = sc.feat_hw
+    nchw = scenes.random_features(sc, seed=0, batch=batch, channels_last=False).to(dev)
+    pts = pj.get_points(sc.n_voxels, sc.voxel_size, origin).to(dev)
+    Pd = P.to(dev)
+    out = {"what": f"stock PyTorch {torch.__version__} / cuDNN {torch.backends.cudnn.version()} on the same GPU, "
+                   f"eager; modules: {what}", "scenes": batch}
+    old = torch.backends.cudnn.allow_tf32
+    with torch.no_grad():
+        def ref_bp():
+            for b in range(batch):
+                scene_volume(nchw[b][:, :, :h, :w], pts, Pd)
+        out["backproject_ms"] = _event_time(ref_bp, reps=2)
+        del nchw
+        if NECKS[workload] is not None:
+            name, kw, _ = NECKS[workload]
+            torch.manual_seed(0)
+            ref = randomize_norms(neck_class(name)(**kw).eval()).to(dev)
+            x = torch.randn((batch, sc.channels) + tuple(sc.n_voxels), device=dev)
+            torch.backends.cudnn.allow_tf32 = True
+            out["neck_cudnn_tf32_ms"] = _event_time(lambda: ref(x), reps=2)
+            refb = ref.to(torch.bfloat16).to(memory_format=torch.channels_last_3d)
+            xb = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last_3d)
+            del x
+            out["neck_cudnn_bf16_channels_last_3d_ms"] = _event_time(lambda: refb(xb), reps=2)
+            del ref, refb, xb
+    torch.backends.cudnn.allow_tf32 = old
+    torch.cuda.empty_cache()
+    return out
+
+
+def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev, peaks):
+    """Strong scaling of one multi-view configuration: the V views of every scene of ONE fixed batch are
+    sharded over the `world` ranks (rank r takes views r, r + world, ...), every rank back-projects its
+    views into partial sums / counts in symmetric memory, `ivx_finalize_mean_peers` reduces them over
+    NVLink and divides (reduce-scatter semantics: each rank finalizes, and runs the bf16 neck on, its own
+    slice of the scenes).  world == 1 gives the single-GPU point of the same curve.  Inputs are generated
+    on the device (seeded per view, identical on every rank); K steps are replayed from one CUDA graph."""
+    from imvoxelnet_b200 import necks, ops, sharding
+    sc, batch, P, origin = scene_setup(name)
+    V, C, N = sc.n_views, sc.channels, sc.n_total_voxels
+    h, w = sc.feat_hw
+    hf, wf = sc.map_hw
+    my_views = sharding.shard_views(V, rank, world)
+    mine = sharding.shard_scenes(batch, rank, world)
+    my_scenes = mine.stop - mine.start
+
+    def view_features(v, scene_slice=slice(None)):      # [b, hf, wf, C]: channels-last maps of view v
+        g = torch.Generator(device=dev)
+        g.manual_seed(1234 + v)
+        return torch.randn((batch, hf, wf, C), generator=g, device=dev)[scene_slice]
+
+    def stack(views, scene_slice=slice(None)):          # logical [b, V', C, hf, wf], NHWC memory
+        if not views:
+            return torch.empty((batch, 0, hf, wf, C), device=dev).permute(0, 1, 4, 2, 3)
+        return torch.stack([view_features(v, scene_slice) for v in views], 1).permute(0, 1, 4, 2, 3)
+
+    feats = stack(my_views)
+    proj = P[my_views].unsqueeze(0).expand(batch, len(my_views), 3, 4).contiguous().to(dev)
+    hws, origins = [(h, w)] * batch, [origin] * batch
+    cls, kw, neck_gflop = NECKS[name]
+    torch.manual_seed(0)
+    neck = randomize_norms(getattr(necks, cls)(**kw).eval()).to(dev)
+    neck.precision = "bf16"
+    fused = None
+    if world > 1:
+        use_mc = collective == "multimem" or (collective == "auto" and world > 2)
+        fused = sharding.FusedViewSharded(batch, C, sc.n_voxels, use_multicast=use_mc)
+
+    def backproject(out_dtype):
+        if fused is not None:
+            return fused(feats, hws, proj, sc.voxel_size, origins, out_dtype=out_dtype, scatter_scenes=True)
+        return ops.backproject_scenes(feats, hws, proj, sc.n_voxels, sc.voxel_size, origins, out_dtype=out_dtype)
+
+    def bp_only(i):
+        return backproject(torch.bfloat16)
+
+    def step(i):
+        vol, valid, _ = backproject(torch.bfloat16)
+        return neck(vol) if vol.shape[0] > 0 else None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    rec = {"workload": sc.name, "scenes_per_step": batch, "views": V, "n_gpus": world,
+           "views_on_rank0": len(my_views), "scenes_finalized_on_rank0": my_scenes, "neck": cls + " (bf16)"}
+    with torch.no_grad():
+        # self-check on rank 0 (all ranks take part in the collective): the sharded fp32 volume of its
+        # scenes against the unsharded kernel on all V views of the same scenes
+        vol32, valid, count = backproject(torch.float32)
+        if world > 1 and rank == 0 and my_scenes > 0:
+            full = stack(list(range(V)), mine)
+            pf = P.unsqueeze(0).expand(my_scenes, V, 3, 4).contiguous().to(dev)
+            ref, ref_valid, ref_count = ops.backproject_scenes(full, hws[:my_scenes], pf, sc.n_voxels, sc.voxel_size,
+                                                               origins[:my_scenes])
+            err = (vol32 - ref).abs().max().item()
+            scale = ref.abs().max().item()
+            rec["self_check"] = {"max_err": err, "max_ref": scale, "within_1e-5": bool(err <= 1e-5 * scale + 1e-6),
+                                 "counts_equal": bool(torch.equal(count, ref_count)),
+                                 "valid_equal": bool(torch.equal(valid, ref_valid))}
+            del full, ref, ref_valid, ref_count
+        del vol32, valid, count
+        for i in range(max(warmup, 3)):
+            step(i)
+        barrier()
+        mode = "cuda-graph replay of K steps, median of 5"
+        try:
+            bp_total, _g1 = timed_graph(bp_only, steps, barrier)
+            total, _g2 = timed_graph(step, steps, barrier)
+        except Exception as exc:            # capture refused (e.g. the symmetric-memory barrier): eager issue
+            torch.cuda.synchronize()
+            mode = f"eager ({type(exc).__name__} during graph capture)"
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            res = []
+            for fn in (bp_only, step):
+                barrier()
+                ev0.record()
+                for i in range(steps):
+                    fn(i)
+                ev1.record()
+                barrier()
+                res.append(ev0.elapsed_time(ev1))
+            bp_total, total = res
+    t = torch.tensor([total, bp_total], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    total, bp_total = (float(v) for v in t.tolist())
+    ms, bp_ms = total / steps, bp_total / steps
+    neck_ms = max(ms - bp_ms, 1e-6)
+    per_rank = -(-batch // world)                                   # scenes the busiest rank ran the neck on
+    tflops = neck_gflop * per_rank / neck_ms
+    peak, peak_kind = tensor_peak(peaks, total)
+    partial_bytes = batch * N * (C + 1) * 4                          # what every rank writes
+    nvlink_in = per_rank * N * (C + 1) * 4 * (world - 1)              # peers' partials of this rank's scenes
+    rec.update({
+        "ms_per_step": ms, "scenes_per_s": batch / (ms * 1e-3), "voxel_views_per_s": batch * V * N / (ms * 1e-3),
+        "timing": mode,
+        "stages": {"backproject_reduce_finalize_ms": bp_ms, "neck_ms": neck_ms},
+        "collective": ("none (one GPU)" if fused is None else
+                       "fused into ivx_finalize_mean_peers: " +
+                       ("multimem.ld_reduce (NVLS)" if fused.multicast else "peer loads over NVLink")),
+        "partial_bytes_written_per_rank": partial_bytes, "nvlink_bytes_read_per_rank": nvlink_in,
+        "nvlink_read_gbs_if_all_of_stage": nvlink_in / (bp_ms * 1e-3) / 1e9 if world > 1 else 0.0,
+        "roofline_neck": {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
+                          "frac": tflops / peak, "peak_kind": "measured " + peak_kind,
+                          "scenes_on_busiest_rank": per_rank}})
+    del fused, neck, feats
+    torch.cuda.empty_cache()
+    return rec
+
+
 def run_ours(args):
     import torch.distributed as dist
     from imvoxelnet_b200 import _lib, conv, necks, ops, sharding
@@ -258,6 +486,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    n_cpus = pin_to_gpu_cpus(local)          # before any pinned allocation: first touch on the near node
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     _lib.lib()  # fail loudly if the CUDA library is missing
@@ -401,6 +630,9 @@ def run_ours(args):
         eager_ms_per_step = ev0.elapsed_time(ev1) / args.steps
 
     scenes_global = batch * (1 if view_sharded else world)
+    # scenes whose neck the busiest rank ran: its scatter slice when the views are sharded through the fused
+    # kernel (reduce-scatter semantics), the whole batch otherwise (own scenes, or replicated after all-reduce)
+    neck_scenes = -(-batch // world) if (view_sharded and fused is not None) else batch
     units_per_step = scenes_global * V * N
     value = units_per_step / (ms_per_step * 1e-3)
     peaks, peak_kind = load_peaks()
@@ -419,25 +651,37 @@ def run_ours(args):
     roofline = roofline_bp
     if neck is not None:
         neck_ms = max(ms_per_step - bp_in_step_ms, 1e-6)   # full step minus its back-projection
-        tflops = neck_gflop * batch / neck_ms                      # GFLOP / ms == TFLOP/s
-        peak = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+        tflops = neck_gflop * neck_scenes / neck_ms                # GFLOP / ms == TFLOP/s, of one rank
+        peak, which_peak = tensor_peak(peaks, total_ms)
+        sustained = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
         stages["neck"] = {"ms": neck_ms, "tflops": tflops, "precision": args.neck_precision,
-                          "gflop_per_scene": neck_gflop, "module": type(neck).__name__}
+                          "gflop_per_scene": neck_gflop, "module": type(neck).__name__,
+                          "scenes_per_rank": neck_scenes}
         if args.neck_precision == "bf16":
             # dominant kernel of the step: conv3d_tc_kernel (tcgen05 implicit GEMM), timed inside a long step
             roofline = {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
-                        "frac": tflops / peak, "frac_of_burst_peak": tflops / peaks["bf16_tflops"],
+                        "frac": tflops / peak, "frac_of_sustained_peak": tflops / sustained,
                         "traffic": _ncu_traffic("neck_" + sc.name),
-                        "kernel": "conv3d_tc_halo_kernel / conv3d_tc_kernel", "peak_kind": peak_kind + " (sustained)",
-                        "algorithmic_flops_per_step": neck_gflop * batch * 1e9,
+                        "kernel": "conv3d_tc_halo_kernel / conv3d_tc_kernel", "peak_kind": f"{peak_kind} {which_peak}",
+                        "algorithmic_flops_per_step": neck_gflop * neck_scenes * 1e9,
                         "launches_per_step": launches // max(args.steps, 1) - 1}
         elif args.neck_precision == "tf32":
             # same kernel with kind::tf32 MMAs; no measured tf32 peak in MEASURED_PEAKS.json: half the
             # bf16 figure is the nominal ratio of the two tensor rates (1.1 vs 2.25 PFLOP/s dense)
             roofline = {"bound": "tensor", "achieved": tflops, "peak": peak / 2, "unit": "TFLOP/s",
-                        "frac": tflops / (peak / 2), "traffic": None, "kernel": "conv3d_tc_kernel<tf32>",
-                        "peak_kind": peak_kind + " (sustained bf16) / 2: nominal tf32 : bf16 ratio",
-                        "algorithmic_flops_per_step": neck_gflop * batch * 1e9,
+                        "frac": tflops / (peak / 2), "traffic": None, "kernel": "conv3d_tc_halo_kernel<tf32> / conv3d_tc_kernel<tf32>",
+                        "peak_kind": f"{peak_kind} bf16 {which_peak} / 2: nominal tf32 : bf16 ratio",
+                        "algorithmic_flops_per_step": neck_gflop * neck_scenes * 1e9,
+                        "launches_per_step": launches // max(args.steps, 1) - 1}
+        elif args.neck_precision == "fp32":
+            # fp32-grade results from three tf32 products per multiply-add (3xTF32): the tensor pipe
+            # does 3x the algorithmic flops at the tf32 rate, so the bound is bf16 peak / 2 / 3
+            roofline = {"bound": "tensor", "achieved": tflops, "peak": peak / 6, "unit": "TFLOP/s",
+                        "frac": tflops / (peak / 6), "traffic": None,
+                        "kernel": "conv3d_tc_halo_kernel<tf32, x3> / conv3d_tc_kernel<tf32, x3>",
+                        "peak_kind": f"{peak_kind} bf16 {which_peak} / 2 (tf32 : bf16) / 3 (tf32 products per fp32-grade product)",
+                        "algorithmic_flops_per_step": neck_gflop * neck_scenes * 1e9,
+                        "tensor_pipe_tflops": 3 * tflops,
                         "launches_per_step": launches // max(args.steps, 1) - 1}
 
     # ---- end to end: host buffers in, host buffers out, every step ----
@@ -472,30 +716,78 @@ def run_ours(args):
             pass
         e1.record()
         barrier()
-    t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        e2e_total = e0.elapsed_time(e1)
+        # the same copies with no kernel between them: what the host link alone allows at this N
+        # (all ranks copy at once, as in the run above)
+        static_out = device_step(runner._dev_in[0][0], runner._dev_in[0][1])
+        copier = StreamedHotPath(lambda feats, pd: static_out)
+        for _ in copier.run(batches(2)):
+            pass
+        barrier()
+        e0.record()
+        for _ in copier.run(batches(e2e_steps)):
+            pass
+        e1.record()
+        barrier()
+        copy_total = e0.elapsed_time(e1)
+        del static_out, copier
+    t = torch.tensor([e2e_total, copy_total], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(t.item()) / e2e_steps
+    e2e_ms, copy_ms = (float(v) / e2e_steps for v in t.tolist())
     e2e = {"value": units_per_step / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps,
            "scenes_per_s": scenes_global / (e2e_ms * 1e-3),
+           "copy_ceiling": {"ms_per_step": copy_ms, "h2d_gbs_per_gpu": h2d / (copy_ms * 1e-3) / 1e9,
+                            "d2h_gbs_per_gpu": d2h / (copy_ms * 1e-3) / 1e9,
+                            "d2h_gbs_all_gpus": world * d2h / (copy_ms * 1e-3) / 1e9,
+                            "what": "the same pinned-host copies in and out on the same streams with no kernel "
+                                    "in between, all ranks at once: the step cannot be shorter than this"},
            "api": "pipeline.StreamedHotPath over ops.backproject_scenes (ivx_backproject_scenes) + neck "
                   "forward (ivx_conv3d_ndhwc*): every step copies pinned host features + projections in "
                   "and the neck outputs + valid mask out to pinned host memory; copies overlap compute "
                   "on side streams"}
 
+    extras = {}
+    if not args.no_extras:
+        with torch.no_grad():
+            if neck is not None and args.neck_precision == "bf16" and not view_sharded:
+                # the same neck at the reference's own precision (fp32, 1e-5 of the reference): 3xTF32 on tcgen05
+                neck.precision = "fp32"
+                vol32 = backproject(dev_sets[0], P_dev, torch.float32)[0]
+                reps = 3
+                fp32_ms = _event_time(lambda: neck(vol32), reps=reps, warm=2)
+                neck.precision = args.neck_precision
+                del vol32
+                burst = peaks["bf16_tflops"]
+                tf = neck_gflop * batch / fp32_ms
+                extras["neck_fp32"] = {
+                    "ms": fp32_ms, "tflops": tf, "precision": "fp32 results (1e-5) from 3 tf32 products on tcgen05",
+                    "roofline": {"bound": "tensor", "achieved": tf, "peak": burst / 6, "unit": "TFLOP/s",
+                                 "frac": tf / (burst / 6),
+                                 "peak_kind": f"{peak_kind} bf16 burst (timed region {reps * fp32_ms / 1e3:.2f} s) / 2 "
+                                              "(tf32 : bf16) / 3 (tf32 products per fp32-grade product)",
+                                 "kernel": "conv3d_tc_halo_kernel<tf32, x3> / conv3d_tc_kernel<tf32, x3> + split_tf32_kernel"}}
+            if world == 1:
+                extras["gpu_reference"] = gpu_reference(sc, batch, P, origin, args.workload, dev)
+            if not view_sharded:
+                del dev_sets
+                torch.cuda.empty_cache()
+                extras["view_sharded"] = [
+                    view_sharded_record(name, args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks)
+                    for name in ("scannet_fast", "nuscenes_refgrid")]
+
     if rank == 0:
         cpu = None
         if world == 1:
-            times = cpu_reference_time(sc, P, origin, args.workload, repeats=2 if neck is not None else 3,
-                                       warmup=1, with_neck=neck is not None)
+            times, kind, what = cpu_reference_time(sc, P, origin, args.workload,
+                                                   repeats=2 if neck is not None else 3, warmup=1,
+                                                   with_neck=neck is not None)
             tcpu = min(times)
             cores = os.cpu_count() or 1
-            cpu = {"value": sc.voxel_views / tcpu, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"best of {len(times)} x 1 scene of {sc.name}: torch-CPU port of the "
-                             f"reference's backproject + view mean"
-                             f"{' + 3D neck' if neck is not None else ''} (oracle/torch_port.py, "
-                             f"oracle/torch_necks.py)",
+            cpu = {"value": sc.voxel_views / tcpu, "unit": UNIT, "cores": cores, "kind": kind,
+                   "sample": f"best of {len(times)} x 1 scene of {sc.name}: backproject + view mean"
+                             f"{' + 3D neck' if neck is not None else ''} by {what}",
                    "ms_per_scene": tcpu * 1e3, "scenes_per_s": 1.0 / tcpu}
         stage_names = ["backproject+view-mean"] + (["3d-neck"] if neck is not None else [])
         line = {
@@ -504,8 +796,9 @@ def run_ours(args):
             "scaling": "strong" if view_sharded else "weak", "vs_baseline": None,
             "dtype": "f32 back-projection" + (f", {args.neck_precision} neck" if neck is not None else ""),
             "data": "synthetic",
-            "config": config_of(sc, batch, world, {
+            "config": config_of(sc, batch, 1 if view_sharded else world, {
                 "stages": stage_names,
+                "cpus_bound_to_this_gpu": n_cpus,
                 "parallelism": (f"views sharded over {world} ranks + " +
                                 ("NCCL all-reduce" if fused is None else
                                  "reduction fused into the finalize kernel (" +
@@ -523,6 +816,7 @@ def run_ours(args):
             "roofline": roofline, "roofline_backproject": roofline_bp, "cpu_baseline": cpu, "e2e": e2e,
             "clocks": clocks, "gpu_launches": launches, "lib": _lib.version(),
         }
+        line.update(extras)
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -560,8 +854,10 @@ def main():
     ap.add_argument("--workload", default="kitti", choices=sorted(WORKLOADS))
     ap.add_argument("--neck-precision", default="bf16", choices=["bf16", "tf32", "fp32"],
                     help="bf16: tcgen05 kernels (1e-2 of the reference); tf32: fp32 tensors, tf32 tensor-core math "
-                         "(5e-3); fp32: CUDA-core parity path (1e-5)")
+                         "(5e-3); fp32: fp32-grade results (1e-5) on the tensor cores, three tf32 products (3xTF32)")
     ap.add_argument("--no-neck", action="store_true", help="time the back-projection stage only")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the side records (neck_fp32, gpu_reference, view_sharded)")
     ap.add_argument("--feature-dtype", default="f32", choices=["f32", "bf16"],
                     help="dtype of the 2D feature maps (the reference's are fp32; bf16 halves the gather)")
     ap.add_argument("--collective", default="auto", choices=["auto", "multimem", "peer", "nccl"],
