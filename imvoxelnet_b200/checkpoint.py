@@ -58,6 +58,11 @@ def fold_conv_bn3d(module):
 
     def walk(m):
         last, n = None, 0
+        if getattr(m, "condition", False):
+            # ConditionalProjection(condition=True) (necks/imvoxelnet.py:289-291) selects between the
+            # convolution and the decoder tensor BEFORE the norm: folding would rescale one branch only
+            raise ValueError("fold_conv_bn3d: a module with condition=True applies its norm to a select of "
+                             "two tensors, not to its convolution; it cannot be folded")
         for name, child in list(m.named_children()):
             if isinstance(child, nn.BatchNorm3d):
                 if last is not None:                  # only a norm that directly follows a convolution
@@ -79,7 +84,7 @@ def fold_conv_bn3d(module):
     for fc in _fused_layers(module):
         if fc.bn is not None and id(fc.bn) in folded:
             fc.bn = None
-            fc._packed = fc._packed_tc = None
+            fc._packed = fc._packed_tc = fc._packed_tf32 = fc._packed_x3 = None
     return count
 
 

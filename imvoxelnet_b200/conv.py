@@ -230,7 +230,11 @@ class FusedConv:
         return p
 
     def wants_autograd(self, x):
-        """Training path: the module is in ``.train()`` mode, or a gradient is wanted for x."""
+        """Training path: a gradient is wanted, or the norm is in ``.train()`` mode -- nn.BatchNorm3d
+        then normalises with batch statistics and updates its running buffers whatever the grad
+        mode (a validation loop that forgot ``.eval()``), so that case runs the training forward too."""
+        if self.bn is not None and self.bn.training:
+            return True
         return torch.is_grad_enabled() and (self.conv.training or x.requires_grad)
 
     def __call__(self, x, residual=None, residual_after_act=False, post_scale=1.0, out_dtype=None):

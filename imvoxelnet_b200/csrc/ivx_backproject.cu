@@ -1028,8 +1028,10 @@ extern "C" int ivx_backproject_scenes_nchw(const float *feat, const int64_t *fea
 // separate finalize pass, one kernel reads the partials of all ranks and
 // divides: through the NVSwitch multicast address with multimem.ld_reduce (the
 // switch adds the G copies and returns one value: NVLS) when the buffer has
-// one, else by loading each peer's copy over NVLink in rank order.  The result
-// is the same on every rank (same summation order everywhere).
+// one, else by loading each peer's copy over NVLink in rank order.  With the
+// peer loads the result is bit-identical on every rank (same summation order
+// everywhere); the switch's own order of the fp32 adds is not specified, so the
+// multicast path only promises the 1e-5 bar.
 // ---------------------------------------------------------------------------
 namespace ivx {
 
@@ -1119,6 +1121,7 @@ extern "C" int ivx_finalize_mean_peers(const float *const *peer_sums, const int3
     IVX_REQUIRE(n_scenes > 0 && n_points > 0 && n_points < (1ll << 31), "sizes out of range");
     IVX_REQUIRE(n_channels > 0 && n_channels % 4 == 0, "partial sums must be channels-last with C %% 4 == 0");
     IVX_REQUIRE(vol_dtype == IVX_F32 || vol_dtype == IVX_BF16, "unknown vol_dtype %d", vol_dtype);
+    IVX_REQUIRE(mc_sum == nullptr || aligned16(mc_sum), "mc_sum must be 16-byte aligned (multimem.ld_reduce.v4.f32)");
     const size_t esz = vol_dtype == IVX_BF16 ? 2 : 4;
     if (vol_strides[1] == 1)
         IVX_REQUIRE(vol_strides[0] % 4 == 0 && vol_strides[2] % 4 == 0 &&

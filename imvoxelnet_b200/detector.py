@@ -16,7 +16,8 @@ from torch import nn
 
 from . import backbone2d, ops
 from . import necks as _necks  # noqa: F401  (importing it registers the four 3D necks)
-from .projection import compute_projection, compute_projection_batch, get_points  # noqa: F401  (get_points is re-exported: heads import it from here, imvoxel_head.py:7)
+from .ops import backproject  # noqa: F401  (module-level function of detectors/imvoxelnet.py:145)
+from .projection import compute_projection, compute_projection_batch, get_extrinsics, get_points  # noqa: F401  (re-exported as in detectors/imvoxelnet.py:133, :164; heads import get_points from here, imvoxel_head.py:7)
 from .registry import DETECTORS, HAVE_MMDET, NECKS, build_from, register
 
 if HAVE_MMDET:  # pragma: no cover
@@ -94,6 +95,11 @@ class ImVoxelNet(_Base):
                     m.init_weights(pretrained=pretrained) if m is self.backbone else m.init_weights()
                 except TypeError:
                     m.init_weights()
+
+    @staticmethod
+    def _compute_projection(img_meta, stride, angles):
+        """Same static method as detectors/imvoxelnet.py:114-129: [V,3,4] fp32 matrices on the CPU."""
+        return compute_projection(img_meta, stride, angles)
 
     def set_precision(self, precision):
         """"fp32" (1e-5 of the reference) or "bf16" (tensor-core neck, 1e-2)."""

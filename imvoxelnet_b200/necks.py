@@ -188,30 +188,46 @@ class _StridedStage(nn.Sequential):
 
 
 class ConditionalProjection(nn.Module):
-    """reference :263-294 with condition=False: relu(bn(conv1x1(x)))."""
+    """reference :263-294: relu(bn(conv1x1(skip))) as one fused layer.  With ``condition=True``
+    (no reference config sets it) the decoder tensor replaces the projected skip where the mask is
+    off *before* the norm (:290-291), so the convolution runs alone and the select / affine / ReLU
+    are element-wise torch ops on the device; inference only."""
 
-    def __init__(self, n):
+    def __init__(self, n, condition=False):
         super().__init__()
         self.conv = nn.Conv3d(n, n, 1, bias=False)
         self.norm = nn.BatchNorm3d(n)
         self.relu = nn.ReLU(True)
+        self.condition = bool(condition)
         self._f = FusedConv(self.conv, self.norm, relu=True)
+        self._raw = FusedConv(self.conv, None, relu=False)
+
+    def conditional_half_sum(self, skip, decoder, mask):
+        """(decoder + relu(bn(where(mask, conv(skip), decoder)))) / 2 on [B,X,Y,Z,C] tensors (:289-294, :367)."""
+        if self.norm.training and torch.is_grad_enabled():
+            raise NotImplementedError("ConditionalProjection(condition=True) is supported in eval mode only")
+        z = torch.where(mask, self._raw(skip).float(), decoder.float())
+        bn = self.norm
+        scale = bn.weight / torch.sqrt(bn.running_var + bn.eps)
+        y = torch.relu(z * scale + (bn.bias - bn.running_mean * scale))
+        return ((decoder.float() + y) / 2).to(decoder.dtype)
 
 
 class EncoderDecoder(nn.Module):
     """reference :297-372 (norm='BN', drop=0, cond_proj=False, zero_init_residual=True)."""
 
-    def __init__(self, channels, layers_down, layers_up):
+    def __init__(self, channels, layers_down, layers_up, cond_proj=False):
         super().__init__()
+        self.cond_proj = bool(cond_proj)
         self.layers_down = nn.ModuleList()
         proj = []
         self.layers_down.append(_Stack(*[BasicBlock3d(channels[0], channels[0])
                                          for _ in range(layers_down[0])]))
-        proj.append(ConditionalProjection(channels[0]))
+        proj.append(ConditionalProjection(channels[0], cond_proj))
         for i in range(1, len(channels)):
             self.layers_down.append(_StridedStage(channels[i - 1], channels[i], layers_down[i]))
             if i < len(channels) - 1:
-                proj.append(ConditionalProjection(channels[i]))
+                proj.append(ConditionalProjection(channels[i], cond_proj))
         self.proj = nn.ModuleList(proj[::-1])
         rev = channels[::-1]
         self.layers_up_conv = nn.ModuleList()
@@ -226,6 +242,8 @@ class EncoderDecoder(nn.Module):
                 nn.init.constant_(m.bn2.weight, 0)
 
     def forward(self, x):
+        if self.cond_proj:      # :347-348, on the channels-last tensor: [B,X,Y,Z,1]
+            valid_mask = (x != 0).any(-1, keepdim=True)
         feats = []
         for layer in self.layers_down:
             x = layer(x)
@@ -233,6 +251,14 @@ class EncoderDecoder(nn.Module):
         feats = feats[::-1]
         outs = []
         for i in range(len(self.layers_up_conv)):
+            if self.cond_proj:
+                # :359-367 with the mask resampled as F.interpolate(scale_factor=1/k) does (nearest: index k*j)
+                x = upsample2x_trilinear(self._up[i](x))
+                k = 2 ** (len(self.layers_up_conv) - i - 1)
+                x = self.proj[i].conditional_half_sum(feats[i + 1], x, valid_mask[:, ::k, ::k, ::k])
+                x = self.layers_up_res[i](x)
+                outs.append(x)
+                continue
             # :359-360 computes conv1x1x1(upsample(x)); a bias-free pointwise conv and trilinear
             # interpolation (weights summing to 1) commute, so the conv runs on the 8x smaller
             # tensor and the up-sampling on the narrower one
@@ -250,9 +276,7 @@ class ImVoxelNeck(_NeckBase):
 
     def __init__(self, channels, out_channels, down_layers, up_layers, conditional):
         super().__init__()
-        if conditional:
-            raise NotImplementedError("conditional=True is used by no reference config")
-        self.model = EncoderDecoder(list(channels), list(down_layers), list(up_layers))
+        self.model = EncoderDecoder(list(channels), list(down_layers), list(up_layers), bool(conditional))
         self.conv_blocks = nn.ModuleList([
             _ConvBnRelu(nn.Conv3d(c, out_channels, 3, padding=1)) for c in channels])
 

@@ -206,9 +206,7 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
     xs, ys, zs = (int(t) for t in n_voxels)
     n = xs * ys * zs
     proj = _proj_dev(projection, dev).reshape(b, v, 12)
-    hw_arr = _lib.i32([int(t) for pair in hw for t in pair])
-    if len(hw_arr) != 2 * b:
-        raise ValueError("hw must hold one (height, width) pair per scene")
+    hw_arr = _hw_arg(hw, b, features.shape[3], features.shape[4])
     if points is not None:
         pts = _points_arg(points, dev)
         pp, g, no = pts.data_ptr(), None, None
@@ -258,6 +256,21 @@ def backproject_scenes(features, hw, projection, n_voxels, voxel_size, origins, 
             count.view(b, xs, ys, zs))
 
 
+def _hw_arg(hw, n_scenes, map_h, map_w):
+    """Host int32 [B][2] array of the per-scene (height, width).  The kernels only get strides, so the
+    extents are checked here against the real feature map: the reference's slice
+    ``feature[:, :, :height, :width]`` (detectors/imvoxelnet.py:69) clamps to the tensor, an
+    unchecked hw beyond it would read (forward) or atomically add (backward) out of bounds."""
+    flat = [int(t) for pair in hw for t in pair]
+    if len(flat) != 2 * n_scenes:
+        raise ValueError("hw must hold one (height, width) pair per scene")
+    for i in range(n_scenes):
+        h, w = flat[2 * i], flat[2 * i + 1]
+        if not (0 < h <= map_h and 0 < w <= map_w):
+            raise ValueError(f"scene {i}: hw = ({h}, {w}) outside the feature map ({map_h}, {map_w})")
+    return _lib.i32(flat)
+
+
 def _backproject_scenes_backward(grad_volume, grad_feat, hw, projection, n_voxels, voxel_size, origins,
                                  points, reduce):
     """grad_feat (zero-filled, channels-last [B,V,C,Hf,Wf]) += scatter of grad_volume [B,C,X,Y,Z]."""
@@ -270,7 +283,7 @@ def _backproject_scenes_backward(grad_volume, grad_feat, hw, projection, n_voxel
     if gv.stride(1) != 1 or gv.stride(2) != c or gv.dtype != torch.float32:
         gv = gv.float().permute(0, 2, 1).contiguous().permute(0, 2, 1)      # NDHWC, dense
     proj = _proj_dev(projection, dev).reshape(b, v, 12)
-    hw_arr = _lib.i32([int(t) for pair in hw for t in pair])
+    hw_arr = _hw_arg(hw, b, grad_feat.shape[3], grad_feat.shape[4])
     if points is not None:
         pts = _points_arg(points, dev)
         pp, g, no = pts.data_ptr(), None, None

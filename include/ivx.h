@@ -114,6 +114,11 @@ IVX_API int ivx_project_indices(const float *points, const ivx_grid *grid,
  *                 reference's NCHW slice of :69) takes the strided kernel.
  *   hw            host [B][2] int32: un-padded (height, width) of each scene's
  *                 map, img_shape // stride (:67-68).  Pixels outside are invalid.
+ *                 PRECONDITION: 0 < height <= Hf and 0 < width <= Wf of the
+ *                 tensor behind `feat` -- the library sees only strides and
+ *                 cannot check it; a larger hw reads (or, in the backward
+ *                 entry point, atomically adds) out of bounds.  The Python
+ *                 mirror (ops.backproject_scenes) checks it against the tensor.
  *   proj          [B][V][12] fp32
  *   points        [3][N] fp32 shared by all scenes, or NULL to use `grid` with
  *                 new_origin (host [B][3]; scenes may have different origins)
@@ -275,7 +280,14 @@ IVX_API int ivx_backproject_scenes_nchw(const float *feat, const int64_t *feat_s
  *
  * First call on each device: the address of the array on that device is
  * looked up (with that device current) and remembered; make this first call
- * before starting any stream capture on that device.
+ * before starting any stream capture on that device.  With CUDA's default lazy
+ * module loading that first call is also when the driver loads this part of
+ * the library onto the device and sets the 32 MiB aside, so make it at
+ * start-up, BEFORE the host application hands the rest of the GPU memory to
+ * its own pool -- afterwards the load itself can fail for lack of memory.
+ * cudaDeviceReset() discards the array together with everything else on the
+ * device and leaves the remembered address stale: do not call this function
+ * again on a device that has been reset in this process.
  *
  * All calls on one device share the array and it keeps what the last call
  * left there.  Nothing needs clearing (each call overwrites every element it

@@ -98,29 +98,37 @@ class ResBlock(nn.Module):
 
 
 class SkipProjection(nn.Module):
-    def __init__(self, c):
+    """necks/imvoxelnet.py:263-294: relu(bn(conv1x1x1(skip))); with `condition` the decoder tensor
+    replaces the projected skip where the mask is off, before the norm (:290-291)."""
+
+    def __init__(self, c, condition=False):
         super().__init__()
         self.conv = nn.Conv3d(c, c, 1, bias=False)
         self.norm = nn.BatchNorm3d(c)
+        self.condition = condition
 
-    def forward(self, x):
-        return F.relu(self.norm(self.conv(x)))
+    def forward(self, x, decoder=None, mask=None):
+        x = self.conv(x)
+        if self.condition:
+            x = torch.where(mask, x, decoder)
+        return F.relu(self.norm(x))
 
 
 class EncoderDecoder(nn.Module):
-    def __init__(self, channels, layers_down, layers_up):
+    def __init__(self, channels, layers_down, layers_up, cond_proj=False):
         super().__init__()
+        self.cond_proj = cond_proj
         self.layers_down = nn.ModuleList()
         proj = []
         self.layers_down.append(nn.Sequential(*[ResBlock(channels[0]) for _ in range(layers_down[0])]))
-        proj.append(SkipProjection(channels[0]))
+        proj.append(SkipProjection(channels[0], cond_proj))
         for i in range(1, len(channels)):
             layer = [nn.Conv3d(channels[i - 1], channels[i], 3, 2, 1, bias=False),
                      nn.BatchNorm3d(channels[i]), nn.Dropout(0, True), nn.ReLU(inplace=True)]
             layer += [ResBlock(channels[i]) for _ in range(layers_down[i])]
             self.layers_down.append(nn.Sequential(*layer))
             if i < len(channels) - 1:
-                proj.append(SkipProjection(channels[i]))
+                proj.append(SkipProjection(channels[i], cond_proj))
         self.proj = nn.ModuleList(proj[::-1])
         rev = channels[::-1]
         self.layers_up_conv = nn.ModuleList()
@@ -133,6 +141,8 @@ class EncoderDecoder(nn.Module):
                 nn.init.constant_(m.bn2.weight, 0)
 
     def forward(self, x):
+        if self.cond_proj:                            # :347-348: voxels with any non-zero input channel
+            valid_mask = (x != 0).any(1, keepdim=True).float()
         feats = []
         for layer in self.layers_down:
             x = layer(x)
@@ -142,7 +152,11 @@ class EncoderDecoder(nn.Module):
         for i in range(len(self.layers_up_conv)):
             x = F.interpolate(x, scale_factor=2, mode='trilinear', align_corners=False)
             x = self.layers_up_conv[i](x)
-            x = (x + self.proj[i](feats[i + 1])) / 2
+            mask = None
+            if self.cond_proj:                        # :361-363: nearest-neighbour resampling of the mask
+                scale = 1 / 2 ** (len(self.layers_up_conv) - i - 1)
+                mask = F.interpolate(valid_mask, scale_factor=scale) != 0
+            x = (x + self.proj[i](feats[i + 1], x, mask)) / 2
             x = self.layers_up_res[i](x)
             outs.append(x)
         return outs
@@ -151,9 +165,7 @@ class EncoderDecoder(nn.Module):
 class ImVoxelNeck(nn.Module):
     def __init__(self, channels, out_channels, down_layers, up_layers, conditional):
         super().__init__()
-        if conditional:
-            raise NotImplementedError("conditional projection is False in every reference config")
-        self.model = EncoderDecoder(list(channels), list(down_layers), list(up_layers))
+        self.model = EncoderDecoder(list(channels), list(down_layers), list(up_layers), bool(conditional))
         self.conv_blocks = nn.ModuleList([_conv_bn_relu(c, out_channels, bias=True) for c in channels])
 
     def forward(self, x):

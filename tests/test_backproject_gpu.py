@@ -398,3 +398,14 @@ def test_bf16_feature_maps_equal_the_widened_maps(name):
     c = ops.backproject_scenes(maps16, [(h, w)], P[None], sc.n_voxels, sc.voxel_size, [origin],
                                out_dtype=torch.bfloat16)
     assert torch.equal(c[0], b[0].to(torch.bfloat16))
+
+
+def test_hw_beyond_the_feature_map_is_refused():
+    """The reference's slice feature[:, :, :h, :w] (:69) clamps to the tensor; the kernels only see
+    strides, so the Python mirror refuses an hw outside the map instead of reading out of bounds."""
+    sc, full, origin, P = _scene_inputs("sunrgbd_fast", seed=3)
+    feats = full.to(DEV)[None]
+    hf, wf = feats.shape[3:]
+    for bad in ((hf + 1, wf), (hf, wf + 1), (0, wf)):
+        with pytest.raises(ValueError, match="outside the feature map"):
+            ops.backproject_scenes(feats, [bad], P[None], sc.n_voxels, sc.voxel_size, [origin])

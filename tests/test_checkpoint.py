@@ -98,3 +98,15 @@ def test_folded_product_neck_matches_the_unfolded_one(name, precision):
     if precision == "fp32":
         for j, o in enumerate(got):
             assert_volume_close(o.cpu().numpy(), g[f"out{j}"], rel=2e-5)
+
+
+def test_fold_refuses_a_conditional_projection():
+    """ConditionalProjection(condition=True) applies its norm to where(mask, conv(x), y)
+    (necks/imvoxelnet.py:289-291): folding the norm into the convolution would be wrong."""
+    import pytest
+
+    from imvoxelnet_b200 import checkpoint, necks
+    m = necks.ImVoxelNeck([4, 8, 16, 32], 4, [1, 1, 1, 1], [1, 1, 1], True)
+    with pytest.raises(ValueError, match="condition=True"):
+        checkpoint.fold_conv_bn3d(m)
+    assert checkpoint.fold_conv_bn3d(necks.ImVoxelNeck([4, 8, 16, 32], 4, [1, 1, 1, 1], [1, 1, 1], False)) > 0

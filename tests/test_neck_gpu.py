@@ -254,3 +254,47 @@ def test_upsample2x_trilinear_matches_interpolate(shape, dtype):
         assert_volume_close(got.cpu().numpy(), want.cpu().numpy(), rel=1e-6)
     else:   # one rounding to bf16 of the fp32 result
         assert_volume_close(got.float().cpu().numpy(), want.cpu().numpy(), rel=4e-3)
+
+
+@pytest.mark.parametrize("precision,rel", [("fp32", 1e-5), ("bf16", BF16_RTOL)])
+def test_conditional_projection(precision, rel):
+    """ImVoxelNeck(conditional=True) against the oracle (pinned to the live reference in
+    tests/test_neck_oracle.py), at toy and at tensor-core channel counts."""
+    for channels, shape in (([4, 8, 16, 32], (1, 4, 16, 8, 8)), ([64, 128, 256, 512], (1, 64, 16, 16, 8))):
+        if precision == "bf16" and channels[0] < 64:
+            continue
+        kw = dict(channels=channels, out_channels=channels[0], down_layers=[1, 2, 3, 4], up_layers=[3, 2, 1],
+                  conditional=True)
+        torch.manual_seed(21)
+        ref = torch_necks.ImVoxelNeck(**kw).eval()
+        torch_necks.randomize_norms(ref, 4)
+        m = necks.ImVoxelNeck(**kw).eval()
+        m.load_state_dict(ref.state_dict())
+        m.precision = precision
+        ref.to(DEV), m.to(DEV)
+        x = torch.randn(shape, device=DEV)
+        x[:, :, torch.rand(shape[2:], device=DEV) < 0.4] = 0
+        with torch.no_grad():
+            want, got = ref(x), m(x)
+        for a, b in zip(got, want):
+            assert_volume_close(a.float().cpu().numpy(), b.cpu().numpy(), rel=rel, atol=1e-6 if precision == "fp32" else 1e-3)
+
+
+def test_train_mode_without_grad_uses_batch_statistics():
+    """A neck left in .train() under torch.no_grad() behaves as nn.BatchNorm3d does: batch statistics
+    and updated running buffers (a validation loop that forgot .eval())."""
+    kw, shape = BIGGER["KittiImVoxelNeck"]
+    torch.manual_seed(2)
+    ref = torch_necks.KittiImVoxelNeck(**kw)
+    torch_necks.randomize_norms(ref, 5)
+    m = necks.KittiImVoxelNeck(**kw)
+    m.load_state_dict(ref.state_dict())
+    ref.to(DEV).train(), m.to(DEV).train()
+    x = torch.randn(shape, device=DEV)
+    with torch.no_grad():
+        want, got = ref(x), m(x)
+    assert_volume_close(got[0].cpu().numpy(), want[0].cpu().numpy(), rel=5e-5)
+    a, b = m.state_dict(), ref.state_dict()
+    for k in a:
+        if "running_mean" in k or "running_var" in k:
+            assert_volume_close(a[k].cpu().numpy(), b[k].cpu().numpy(), rel=5e-5)

@@ -73,3 +73,47 @@ def test_necks_refuse_cpu_and_training_mode():
     m.precision = "fp32"
     with pytest.raises(_lib.IvxError):
         m.eval()(torch.zeros(1, 4, 4, 4, 12))
+
+
+def _conditional_case():
+    kw = dict(channels=[4, 8, 16, 32], out_channels=4, down_layers=[1, 2, 3, 4], up_layers=[3, 2, 1],
+              conditional=True)
+    torch.manual_seed(21)
+    x = torch.randn(1, 4, 16, 8, 8)
+    x[:, :, torch.rand(16, 8, 8) < 0.4] = 0          # unobserved voxels: every channel zero (:347-348)
+    return kw, x
+
+
+@pytest.mark.skipif(not ref_loader.available(), reason="reference tree not present on this machine")
+def test_oracle_conditional_projection_matches_live_reference():
+    """ImVoxelNeck(conditional=True) (necks/imvoxelnet.py:281-294, :347-348, :361-363): no reference
+    config sets it, but it is a constructor argument of the drop-in class."""
+    _, ref = ref_loader.load()
+    kw, x = _conditional_case()
+    r = ref.ImVoxelNeck(**kw).eval()
+    torch_necks.randomize_norms(r, 4)
+    m = torch_necks.ImVoxelNeck(**kw).eval()
+    m.load_state_dict(r.state_dict())
+    with torch.no_grad():
+        a, b = r(x), m(x)
+        plain = torch_necks.ImVoxelNeck(**dict(kw, conditional=False)).eval()
+        plain.load_state_dict(r.state_dict())
+        c = plain(x)
+    for u, v in zip(a, b):
+        assert torch.equal(u, v)
+    assert not torch.equal(a[0], c[0])               # the condition changes the result
+
+
+def test_detector_module_mirrors_the_reference_surface():
+    """detectors/imvoxelnet.py exposes get_points (:133), backproject (:145), get_extrinsics (:164)
+    at module level and ImVoxelNet._compute_projection as a static method (:114)."""
+    import inspect
+
+    from imvoxelnet_b200 import detector, ops, projection, scenes
+    assert detector.backproject is ops.backproject
+    assert detector.get_extrinsics is projection.get_extrinsics
+    assert detector.get_points is projection.get_points
+    assert isinstance(inspect.getattr_static(detector.ImVoxelNet, "_compute_projection"), staticmethod)
+    sc = scenes.build("scannet_fast")
+    a = detector.ImVoxelNet._compute_projection(sc.img_meta, 4, None)
+    assert torch.equal(a, projection.compute_projection(sc.img_meta, 4, None))
