@@ -353,15 +353,20 @@ def gpu_reference(sc, batch, P, origin, workload, dev):
     return out
 
 
-def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev, peaks):
+def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev, peaks, scenes_per_rank=None):
     """Strong scaling of one multi-view configuration: the V views of every scene of ONE fixed batch are
     sharded over the `world` ranks (rank r takes views r, r + world, ...), every rank back-projects its
     views into partial sums / counts in symmetric memory, `ivx_finalize_mean_peers` reduces them over
     NVLink and divides (reduce-scatter semantics: each rank finalizes, and runs the bf16 neck on, its own
     slice of the scenes).  world == 1 gives the single-GPU point of the same curve.  Inputs are generated
-    on the device (seeded per view, identical on every rank); K steps are replayed from one CUDA graph."""
+    on the device (seeded per view, identical on every rank); K steps are replayed from one CUDA graph.
+    `scenes_per_rank` (throughput mode): the step holds scenes_per_rank * world scenes, so
+    that after the scatter every rank runs its neck on a full batch; compare with the one-GPU record
+    through scenes_per_s."""
     from imvoxelnet_b200 import necks, ops, sharding
     sc, batch, P, origin = scene_setup(name)
+    if scenes_per_rank is not None:
+        batch = scenes_per_rank * world
     V, C, N = sc.n_views, sc.channels, sc.n_total_voxels
     h, w = sc.feat_hw
     hf, wf = sc.map_hw
@@ -409,6 +414,8 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
         torch.cuda.synchronize()
 
     rec = {"workload": sc.name, "scenes_per_step": batch, "views": V, "n_gpus": world,
+           "mode": ("strong scaling: one fixed batch" if scenes_per_rank is None else
+                    f"throughput: {scenes_per_rank} scenes per rank in flight, views still sharded"),
            "views_on_rank0": len(my_views), "scenes_finalized_on_rank0": my_scenes, "neck": cls + " (bf16)"}
     with torch.no_grad():
         # self-check on rank 0 (all ranks take part in the collective): the sharded fp32 volume of its
@@ -776,6 +783,10 @@ def run_ours(args):
                 extras["view_sharded"] = [
                     view_sharded_record(name, args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks)
                     for name in ("scannet_fast", "nuscenes_refgrid")]
+                if world > 1:
+                    extras["view_sharded"].append(view_sharded_record(
+                        "scannet_fast", args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks,
+                        scenes_per_rank=WORKLOADS["scannet_fast"][1]))
 
     if rank == 0:
         cpu = None
