@@ -391,22 +391,58 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
     torch.manual_seed(0)
     neck = randomize_norms(getattr(necks, cls)(**kw).eval()).to(dev)
     neck.precision = "bf16"
-    fused = None
+    fused, lanes = None, []
     if world > 1:
         use_mc = collective == "multimem" or (collective == "auto" and world > 2)
-        fused = sharding.FusedViewSharded(batch, C, sc.n_voxels, use_multicast=use_mc)
+        # two sets of partial-sum buffers ("lanes"): consecutive steps alternate between them, so the
+        # exchange of one step can overlap the neck of the step before it (pipelined timing below)
+        lanes = [sharding.FusedViewSharded(batch, C, sc.n_voxels, use_multicast=use_mc) for _ in range(2)]
+        fused = lanes[0]
 
-    def backproject(out_dtype):
+    def backproject(out_dtype, lane=0):
         if fused is not None:
-            return fused(feats, hws, proj, sc.voxel_size, origins, out_dtype=out_dtype, scatter_scenes=True)
+            return lanes[lane](feats, hws, proj, sc.voxel_size, origins, out_dtype=out_dtype, scatter_scenes=True)
         return ops.backproject_scenes(feats, hws, proj, sc.n_voxels, sc.voxel_size, origins, out_dtype=out_dtype)
 
     def bp_only(i):
         return backproject(torch.bfloat16)
 
-    def step(i):
-        vol, valid, _ = backproject(torch.bfloat16)
+    def step(i, lane=0):
+        vol, valid, _ = backproject(torch.bfloat16, lane)
         return neck(vol) if vol.shape[0] > 0 else None
+
+    def timed_pipelined(repeats=5):
+        """K steps in one CUDA graph, alternating between two streams (and the two buffer sets): step i + 1's
+        back-projection, barriers and NVLink reduction may run while step i's neck still does."""
+        graph = torch.cuda.CUDAGraph()
+        main = torch.cuda.Stream()
+        side = [torch.cuda.Stream(), torch.cuda.Stream()]
+        main.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(main):
+            with torch.cuda.graph(graph, stream=main):
+                fork = torch.cuda.Event()
+                fork.record(main)
+                for st in side:
+                    st.wait_event(fork)
+                for i in range(steps):
+                    with torch.cuda.stream(side[i % 2]):
+                        step(i, i % 2)
+                for st in side:
+                    join = torch.cuda.Event()
+                    join.record(st)
+                    main.wait_event(join)
+        torch.cuda.current_stream().wait_stream(main)
+        graph.replay()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        totals = []
+        for _ in range(repeats):
+            barrier()
+            ev0.record()
+            graph.replay()
+            ev1.record()
+            barrier()
+            totals.append(ev0.elapsed_time(ev1))
+        return statistics.median(totals), graph
 
     def barrier():
         if world > 1:
@@ -434,12 +470,15 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
             del full, ref, ref_valid, ref_count
         del vol32, valid, count
         for i in range(max(warmup, 3)):
-            step(i)
+            step(i, i % 2 if lanes else 0)
         barrier()
         mode = "cuda-graph replay of K steps, median of 5"
+        pipelined_total = None
         try:
             bp_total, _g1 = timed_graph(bp_only, steps, barrier)
             total, _g2 = timed_graph(step, steps, barrier)
+            if lanes and os.environ.get("IVX_BENCH_PIPELINED", "1") != "0":
+                pipelined_total, _g3 = timed_pipelined()
         except Exception as exc:            # capture refused (e.g. the symmetric-memory barrier): eager issue
             torch.cuda.synchronize()
             mode = f"eager ({type(exc).__name__} during graph capture)"
@@ -454,11 +493,17 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
                 barrier()
                 res.append(ev0.elapsed_time(ev1))
             bp_total, total = res
-    t = torch.tensor([total, bp_total], device=dev, dtype=torch.float64)
+    t = torch.tensor([total, bp_total, pipelined_total if pipelined_total is not None else -1.0], device=dev,
+                     dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total, bp_total = (float(v) for v in t.tolist())
+    total, bp_total, pipelined_total = (float(v) for v in t.tolist())
     ms, bp_ms = total / steps, bp_total / steps
+    if pipelined_total > 0:
+        rec["pipelined"] = {"ms_per_step": pipelined_total / steps,
+                            "scenes_per_s": batch / (pipelined_total / steps * 1e-3),
+                            "what": "the same K steps, consecutive steps on two streams with two sets of "
+                                    "partial-sum buffers: a step's NVLink reduction overlaps the previous step's neck"}
     neck_ms = max(ms - bp_ms, 1e-6)
     per_rank = -(-batch // world)                                   # scenes the busiest rank ran the neck on
     tflops = neck_gflop * per_rank / neck_ms
@@ -477,7 +522,7 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
         "roofline_neck": {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
                           "frac": tflops / peak, "peak_kind": "measured " + peak_kind,
                           "scenes_on_busiest_rank": per_rank}})
-    del fused, neck, feats
+    del fused, lanes, neck, feats
     torch.cuda.empty_cache()
     return rec
 

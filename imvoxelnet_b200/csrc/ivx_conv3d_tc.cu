@@ -535,7 +535,7 @@ static void pick_box(const int32_t out[3], const int32_t stride[3], int box[3], 
 }
 
 // ivx_conv3d_tc_halo.cu
-double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out);
+double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out, double *cost_out = nullptr);
 int launch_conv3d_tc_halo(const ivx_conv3d_params *p, const int perm[3], int mt, const void *x,
                           const void *weight_bf16, const float *scale, const float *shift,
                           const void *residual, void *y, cudaStream_t stream);
@@ -570,6 +570,8 @@ static int validate_tc(const ivx_conv3d_params *p, bool has_residual, bool free_
     return IVX_OK;
 }
 
+static void plan_tc(const ivx_conv3d_params *p, TcArgs &a);
+
 // does the halo-reuse kernel take this layer?  (IVX_TC_HALO=0 keeps everything on the per-tap one)
 static bool use_halo(const ivx_conv3d_params *p, int perm[3], int *mt) {
     static const bool halo_on = [] {
@@ -580,10 +582,32 @@ static bool use_halo(const ivx_conv3d_params *p, int perm[3], int *mt) {
         const char *e = getenv("IVX_HALO_MAX_COUT");
         return e ? atoi(e) : 1024;
     }();
-    // with one tile per CTA (mt == 1) an MMA covers only 128 voxels, i.e. half the tensor rate:
-    // still a win for <= 128 channels (the per-tap kernel is at half rate there too), not above
-    return halo_on && p->c_out <= halo_max_cout && plan_halo(p, perm, mt) >= 0.7 &&
-           (*mt == 2 || p->c_out <= 128);
+    static const bool by_score = [] {
+        const char *e = getenv("IVX_HALO_PLAN");
+        return e != nullptr && e[0] == 's';
+    }();
+    if (!halo_on || p->c_out > halo_max_cout) return false;
+    double halo_cost = 0.0;
+    const double eff = plan_halo(p, perm, mt, &halo_cost);
+    if (eff <= 0.0) return false;
+    if (by_score)
+        // old rule: with one tile per CTA (mt == 1) an MMA covers only 128 voxels, i.e. half the tensor rate:
+        // still a win for <= 128 channels (the per-tap kernel is at half rate there too), not above
+        return eff >= 0.7 && (*mt == 2 || p->c_out <= 128);
+    // the same unit (M128 MMA issue slots per CTA) for the per-tap kernel: it re-reads its activation box for
+    // every tap through L2, which measured at about half the MMA rate of the halo kernel (x 2); its MMAs
+    // have N = n_tile <= 256 columns, the halo kernel's 128 lanes hold min(c_out, 128) channels
+    TcArgs a;
+    plan_tc(p, a);
+    // Measured (ncu launch lists of the four necks at batch 1 / 2 / 8 / 32, profiles/planner_r2.txt): with
+    // 256-channel tiles the per-tap kernel runs within 1.3x of its MMA slots, with 128 / 64-channel tiles
+    // (half / quarter of the columns of an MMA) it is also bound by the L2 -> shared-memory traffic;
+    // a split-K item pays ~30 k-steps per 64 channels for the fp32 atomics and the read-back.
+    const double pen = a.n_tile >= 256 ? 1.3 : 1.5;
+    const double tap_cost = (double)((a.n_tiles + kNumSMs - 1) / kNumSMs) * a.steps_per_split * 4.0 * pen + 50.0 +
+                            (a.k_splits > 1 ? 4.0 * 30.0 * a.n_tile / 64.0 : 0.0);
+    // both costs count whole tiles of their own shape, so they compare directly
+    return halo_cost <= tap_cost;
 }
 
 // tiling of the per-tap kernel, including the split-K decision
@@ -626,7 +650,9 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     {
         auto cost = [&](int splits, int steps) {
             const long long waves = (out_tiles * splits + kNumSMs - 1) / kNumSMs;
-            return (double)waves * (steps + 2.0) * (1.0 + 0.03 * (splits - 1));   // + 2: per-item epilogue
+            // + 2: per-item epilogue; a split item also adds its 128 x n_tile fp32 partials with vector
+            // atomics and the last one reads them back: ~30 k-steps per 64 channels (measured, batch-1 necks)
+            return (double)waves * (steps + 2.0 + (splits > 1 ? 30.0 * a.n_tile / 64.0 : 0.0));
         };
         double best = cost(1, k_steps);
         for (int want = 2; want <= 8 && want * 4 <= k_steps; ++want) {           // at least 4 k-steps per CTA

@@ -392,8 +392,9 @@ conv3d_tc_halo_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_co
 
 // Decide whether (and how) the halo kernel takes a layer.  perm[role] = tensor axis (0=X,1=Y,2=Z)
 // playing role P, Q, R.  Returns the fraction of accumulator rows that hold real outputs, or 0.
-double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
+double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out, double *cost_out) {
     const int ek = p->in_dtype == IVX_BF16 ? 64 : 32;    // channels per 128-byte row: bf16 / tf32
+    if (cost_out) *cost_out = 0.0;
     if (p->transposed || p->c_in % ek != 0 || p->c_out % 64 != 0) return 0.0;
     int strided_axis = -1;
     for (int d = 0; d < 3; ++d) {
@@ -403,7 +404,22 @@ double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
             strided_axis = d;
         }
     }
-    double best = 0.0;
+    // Cost of a plan in MMA issue slots: every CTA tile (8 x 16*mt voxels of one plane -- of two planes for
+    // 64-channel layers -- x 128 accumulator lanes) takes the same number of M128 MMAs whatever mt is (one
+    // M = 128 MMA costs ~128 cycles for N = 128 and for N = 256), the persistent grid runs
+    // ceil(tiles / 148) of them per CTA, plus a fixed pipeline fill + last epilogue.  Wave quantisation
+    // matters for single scenes (200 tiles = 2 waves).  Ties: fewer wasted rows, then P along Z.
+    static const bool by_score = [] {
+        const char *e = getenv("IVX_HALO_PLAN");
+        return e != nullptr && e[0] == 's';
+    }();
+    const int n_tile = p->c_out % 128 == 0 ? 128 : 64;
+    const int n_splits = p->c_out / n_tile;
+    const int chunks = (p->c_in / ek) * (p->in_dtype == IVX_F32X2 ? 3 : 1);
+    double best = 0.0, best_cost = 0.0, best_eff = 0.0, min_cost = 1e300;
+    // pass 0 finds the cheapest plan, pass 1 picks among the plans within 3 % of it by the rule the large
+    // grids were tuned with (few wasted rows, two tiles per CTA, P along the contiguous Z axis)
+    for (int pass = by_score ? 1 : 0; pass < 2; ++pass)
     for (int P = 0; P < 3; ++P)
         for (int Q = 0; Q < 3; ++Q) {
             if (Q == P) continue;
@@ -413,21 +429,29 @@ double plan_halo(const ivx_conv3d_params *p, int perm[3], int *mt_out) {
                 const long long tp = (p->out_dims[P] + HL_P - 1) / HL_P;
                 const long long tq = (p->out_dims[Q] + HL_QT * mt - 1) / (HL_QT * mt);
                 double eff = (double)p->out_dims[P] * p->out_dims[Q] / (double)(tp * HL_P * tq * HL_QT * mt);
-                // sharing a weight slice between two tiles is worth a few wasted rows;
-                // P along the contiguous Z axis keeps the TMA rows contiguous in memory
+                const bool pack2 = n_tile == 64 && p->stride[R] == 1;
+                const long long tr = pack2 ? (p->out_dims[R] + 1) / 2 : p->out_dims[R];
+                const long long tiles = (long long)p->batch * tp * tq * tr * n_splits;
+                const double per_tile = (pack2 ? 36.0 : 27.0) * chunks * 4.0;      // MMAs of one CTA tile
+                const double cost = (double)((tiles + kNumSMs - 1) / kNumSMs) * per_tile + 50.0;
+                // old rule (IVX_HALO_PLAN=score): sharing a weight slice between two tiles is worth a few
+                // wasted rows; P along the contiguous Z axis keeps the TMA rows contiguous in memory
+                if (pass == 0) {
+                    if (cost < min_cost) min_cost = cost;
+                    continue;
+                }
+                if (!by_score && cost > 1.03 * min_cost) continue;
                 const double score = eff * (mt == 2 ? 1.12 : 1.0) * (P == 2 ? 1.02 : 1.0);
                 if (score > best) {
-                    best = score;
+                    best = score, best_cost = cost, best_eff = eff;
                     perm[0] = P, perm[1] = Q, perm[2] = R;
                     *mt_out = mt;
                 }
             }
         }
     if (best == 0.0) return 0.0;
-    // report the plain efficiency of the chosen plan
-    const long long tp = (p->out_dims[perm[0]] + HL_P - 1) / HL_P;
-    const long long tq = (p->out_dims[perm[1]] + HL_QT * *mt_out - 1) / (HL_QT * *mt_out);
-    return (double)p->out_dims[perm[0]] * p->out_dims[perm[1]] / (double)(tp * HL_P * tq * HL_QT * *mt_out);
+    if (cost_out) *cost_out = best_cost;
+    return best_eff;   // fraction of accumulator rows that hold real outputs
 }
 
 template <bool TF32, bool X3 = false>

@@ -134,7 +134,7 @@ def test_tensor_core_transposed_conv(cin, cout, dims, batch):
 
 
 @pytest.mark.parametrize("cin,cout,dims,stride,batch", [(1024, 1024, (10, 10, 4), 1, 1), (1024, 128, (10, 10, 4), 1, 2),
-                                                         (512, 1024, (20, 20, 8), 2, 1), (512, 512, (20, 20, 8), 1, 1)])
+                                                         (512, 1024, (20, 20, 8), 2, 1), (512, 128, (20, 20, 8), 1, 1)])
 def test_split_k_tail_layers_and_workspace_reuse(cin, cout, dims, stride, batch):
     """Few-tile layers split their k-steps over several CTAs through an fp32 workspace;
     the workspace must come back zeroed: three calls in a row give the same result."""

@@ -46,6 +46,7 @@ def main():
     ap.add_argument("--batch", type=int, default=8)
     ap.add_argument("--precision", default="bf16")
     ap.add_argument("--layers", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="also time the forward replayed from a CUDA graph")
     ap.add_argument("--torch-ref", action="store_true")
     ap.add_argument("--train", action="store_true", help="time forward + backward in training mode (fp32)")
     args = ap.parse_args()
@@ -149,6 +150,17 @@ def main():
         print("sum of layers %.3f ms" % total)
     with torch.no_grad():
         ms = timed(lambda: m(x))
+        if args.graph:       # the same forward replayed from a CUDA graph (no host launch gaps)
+            g = torch.cuda.CUDAGraph()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                m(x)
+                with torch.cuda.graph(g, stream=side):
+                    for _ in range(10):
+                        m(x)
+            torch.cuda.current_stream().wait_stream(side)
+            out["graph_ms"] = timed(g.replay, reps=5, warm=2) / 10
     out["ms"] = ms
     out["tflops"] = gflop * args.batch / ms
     out["frac_of_bf16_burst_peak"] = out["tflops"] / 1616.4
