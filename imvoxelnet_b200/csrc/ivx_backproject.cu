@@ -1068,48 +1068,90 @@ __device__ __forceinline__ int multimem_sum_s32(const int32_t *p) {
     return v;
 }
 
+// Each thread keeps FU 16-byte units in flight.  On the multimem path the grid is at most two CTAs per SM
+// (kPeerCtasPerSm): the kernel is then bound by NVLink, not by the SMs, a small grid with more loads per thread
+// moves the same bytes and leaves room on every SM for a CTA of the 3D-neck kernels (one per SM, all of its
+// shared memory, <= 41 K registers), so that a pipelined caller can overlap this reduction with the neck of
+// the previous step.  The view count of
+// a voxel is fetched by one lane per row and warp and passed on with a shuffle (every lane of the row asked
+// for it before: C / 4 identical requests per voxel through the switch).
+constexpr int kPeerCtasPerSm = 2;
+constexpr int FU = 4;
+
 __global__ void __launch_bounds__(256) finalize_mean_peers_kernel(
     const __grid_constant__ PeerArgs pa, long long n_rows, int c4, int N, void *vol, long long os_b,
     long long os_c, long long os_n, int dtype, uint8_t *__restrict__ valid, int32_t *__restrict__ count_out) {
     const long long total = n_rows * c4;
-    for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        const long long row = i / c4;
-        const int q = (int)(i - row * c4);
-        int cnt = 0;
-        float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const int lane = threadIdx.x & 31;
+    for (long long i0 = blockIdx.x * (long long)blockDim.x + threadIdx.x; i0 - threadIdx.x < total; i0 += stride * FU) {
+        float4 s[FU];
+        int cnt[FU];
+        long long row[FU];
+        int q[FU];
+        bool ok[FU];
+#pragma unroll
+        for (int u = 0; u < FU; ++u) {
+            const long long i = i0 + u * stride;
+            ok[u] = i < total;
+            row[u] = ok[u] ? i / c4 : 0;
+            q[u] = ok[u] ? (int)(i - row[u] * c4) : 0;
+            s[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            cnt[u] = 0;
+        }
         if (pa.mc_sum != nullptr) {
-            s = multimem_sum_f32x4(pa.mc_sum + i);
-            cnt = multimem_sum_s32(pa.mc_count + row);
+#pragma unroll
+            for (int u = 0; u < FU; ++u)
+                if (ok[u]) s[u] = multimem_sum_f32x4(pa.mc_sum + i0 + u * stride);
         } else {
             for (int r = 0; r < pa.world; ++r) {   // rank order: the same sum on every rank
-                const float4 t = __ldcs(pa.sum[r] + i);
-                s.x += t.x, s.y += t.y, s.z += t.z, s.w += t.w;
-                cnt += __ldg(pa.count[r] + row);
+                float4 t[FU];
+#pragma unroll
+                for (int u = 0; u < FU; ++u)
+                    t[u] = ok[u] ? __ldcs(pa.sum[r] + i0 + u * stride) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < FU; ++u) s[u].x += t[u].x, s[u].y += t[u].y, s[u].z += t[u].z, s[u].w += t[u].w;
             }
         }
-        const float c = (float)cnt;
-        s.x = cnt ? __fdiv_rn(s.x, c) : 0.f;
-        s.y = cnt ? __fdiv_rn(s.y, c) : 0.f;
-        s.z = cnt ? __fdiv_rn(s.z, c) : 0.f;
-        s.w = cnt ? __fdiv_rn(s.w, c) : 0.f;
-        const long long b = row / N, n = row - b * N;
-        const long long base = b * os_b + n * os_n;
-        if (os_c == 1) {
-            if (dtype == IVX_F32)
-                store4<float>(reinterpret_cast<float *>(vol) + base + q * 4, s);
-            else
-                store4<__nv_bfloat16>(reinterpret_cast<__nv_bfloat16 *>(vol) + base + q * 4, s);
-        } else {
-            float *o = reinterpret_cast<float *>(vol) + base + (long long)q * 4 * os_c;
-            o[0] = s.x;
-            o[os_c] = s.y;
-            o[2 * os_c] = s.z;
-            o[3 * os_c] = s.w;
+#pragma unroll
+        for (int u = 0; u < FU; ++u) {
+            // the first lane of this warp that works on the same row fetches the count for all of them
+            const int src = max(lane - q[u], 0);
+            int c = 0;
+            if (ok[u] && src == lane) {
+                if (pa.mc_sum != nullptr) c = multimem_sum_s32(pa.mc_count + row[u]);
+                else
+                    for (int r = 0; r < pa.world; ++r) c += __ldg(pa.count[r] + row[u]);
+            }
+            cnt[u] = __shfl_sync(0xffffffffu, c, src);
         }
-        if (q == 0) {
-            if (valid) valid[row] = cnt > 0;
-            if (count_out) count_out[row] = cnt;
+#pragma unroll
+        for (int u = 0; u < FU; ++u) {
+            if (!ok[u]) continue;
+            const float c = (float)cnt[u];
+            float4 v = s[u];
+            v.x = cnt[u] ? __fdiv_rn(v.x, c) : 0.f;
+            v.y = cnt[u] ? __fdiv_rn(v.y, c) : 0.f;
+            v.z = cnt[u] ? __fdiv_rn(v.z, c) : 0.f;
+            v.w = cnt[u] ? __fdiv_rn(v.w, c) : 0.f;
+            const long long b = row[u] / N, n = row[u] - b * N;
+            const long long base = b * os_b + n * os_n;
+            if (os_c == 1) {
+                if (dtype == IVX_F32)
+                    store4<float>(reinterpret_cast<float *>(vol) + base + q[u] * 4, v);
+                else
+                    store4<__nv_bfloat16>(reinterpret_cast<__nv_bfloat16 *>(vol) + base + q[u] * 4, v);
+            } else {
+                float *o = reinterpret_cast<float *>(vol) + base + (long long)q[u] * 4 * os_c;
+                o[0] = v.x;
+                o[os_c] = v.y;
+                o[2 * os_c] = v.z;
+                o[3 * os_c] = v.w;
+            }
+            if (q[u] == 0) {
+                if (valid) valid[row[u]] = cnt[u] > 0;
+                if (count_out) count_out[row[u]] = cnt[u];
+            }
         }
     }
 }
@@ -1149,8 +1191,12 @@ extern "C" int ivx_finalize_mean_peers(const float *const *peer_sums, const int3
     }
     const long long rows = (long long)n_scenes * n_points;
     const int c4 = n_channels / 4;
-    long long gx = (rows * c4 + 255) / 256;
-    if (gx > kNumSMs * 32) gx = kNumSMs * 32;
+    long long gx = (rows * c4 + 256 * FU - 1) / (256 * FU);
+    // through the switch (multimem) a rank takes in only its own slice, already reduced: two CTAs per SM keep
+    // the links busy.  Peer loads read every rank's copy, the local one at HBM speed: they need the big grid
+    // (measured at 2 GPUs: 0.53 ms with it, 0.72 ms with two CTAs per SM)
+    const long long max_ctas = (long long)kNumSMs * (mc_sum != nullptr ? kPeerCtasPerSm : 16);
+    if (gx > max_ctas) gx = max_ctas;
     finalize_mean_peers_kernel<<<(unsigned)gx, 256, 0, (cudaStream_t)stream>>>(
         pa, rows, c4, (int)n_points, volume, vol_strides[0], vol_strides[1], vol_strides[2], vol_dtype, valid,
         count_out);
