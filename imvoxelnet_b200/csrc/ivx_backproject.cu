@@ -1069,15 +1069,16 @@ __device__ __forceinline__ int multimem_sum_s32(const int32_t *p) {
 }
 
 // Each thread keeps FU 16-byte units in flight.  On the multimem path the grid is at most two CTAs per SM
-// (kPeerCtasPerSm): the kernel is then bound by NVLink, not by the SMs, a small grid with more loads per thread
-// moves the same bytes and leaves room on every SM for a CTA of the 3D-neck kernels (one per SM, all of its
-// shared memory, <= 41 K registers), so that a pipelined caller can overlap this reduction with the neck of
-// the previous step.  The view count of
+// (kPeerCtasPerSm): the kernel is then bound by NVLink, not by the SMs, and a small grid with more loads per
+// thread moves the same bytes (measured at 8 GPUs: 0.50 ms per step either way).  It was meant to let a
+// pipelined caller overlap this reduction with the neck kernels of the previous step; tools/overlap_probe.py
+// shows that a neck layer and this kernel do not share SMs productively (layer 0.52 ms + reduction 2.85 ms
+// = 4.18 ms together), so pipelining gains what the two streams' other gaps give, not the reduction time.  The view count of
 // a voxel is fetched by one lane per row and warp and passed on with a shuffle (every lane of the row asked
 // for it before: C / 4 identical requests per voxel through the switch).
 constexpr int kPeerCtasPerSm = 2;
-constexpr int FU = 4;
 
+template <int FU>
 __global__ void __launch_bounds__(256) finalize_mean_peers_kernel(
     const __grid_constant__ PeerArgs pa, long long n_rows, int c4, int N, void *vol, long long os_b,
     long long os_c, long long os_n, int dtype, uint8_t *__restrict__ valid, int32_t *__restrict__ count_out) {
@@ -1191,15 +1192,27 @@ extern "C" int ivx_finalize_mean_peers(const float *const *peer_sums, const int3
     }
     const long long rows = (long long)n_scenes * n_points;
     const int c4 = n_channels / 4;
-    long long gx = (rows * c4 + 256 * FU - 1) / (256 * FU);
-    // through the switch (multimem) a rank takes in only its own slice, already reduced: two CTAs per SM keep
-    // the links busy.  Peer loads read every rank's copy, the local one at HBM speed: they need the big grid
-    // (measured at 2 GPUs: 0.53 ms with it, 0.72 ms with two CTAs per SM)
-    const long long max_ctas = (long long)kNumSMs * (mc_sum != nullptr ? kPeerCtasPerSm : 16);
-    if (gx > max_ctas) gx = max_ctas;
-    finalize_mean_peers_kernel<<<(unsigned)gx, 256, 0, (cudaStream_t)stream>>>(
-        pa, rows, c4, (int)n_points, volume, vol_strides[0], vol_strides[1], vol_strides[2], vol_dtype, valid,
-        count_out);
+    // through the switch (multimem) a rank takes in only its own slice, already reduced: two CTAs per SM with
+    // four units per thread keep the links busy.  Peer loads read every rank's copy, the local one at HBM
+    // speed: they keep one unit per thread and the big grid (measured at 2 GPUs: 0.53 ms against 0.61 ms with
+    // four units per thread, 0.72 ms with two CTAs per SM)
+    static const int force_small = [] {           // experiments: the small grid on the peer path too
+        const char *e = getenv("IVX_FINALIZE_SMALL_GRID");
+        return e ? atoi(e) : 0;
+    }();
+    if (mc_sum != nullptr) {
+        long long gx = (rows * c4 + 256 * 4 - 1) / (256 * 4);
+        if (gx > kNumSMs * kPeerCtasPerSm) gx = kNumSMs * kPeerCtasPerSm;
+        finalize_mean_peers_kernel<4><<<(unsigned)gx, 256, 0, (cudaStream_t)stream>>>(
+            pa, rows, c4, (int)n_points, volume, vol_strides[0], vol_strides[1], vol_strides[2], vol_dtype, valid,
+            count_out);
+    } else {
+        long long gx = (rows * c4 + 255) / 256;
+        if (gx > kNumSMs * 32) gx = kNumSMs * 32;
+        finalize_mean_peers_kernel<1><<<(unsigned)gx, 256, 0, (cudaStream_t)stream>>>(
+            pa, rows, c4, (int)n_points, volume, vol_strides[0], vol_strides[1], vol_strides[2], vol_dtype, valid,
+            count_out);
+    }
     IVX_CHECK_LAUNCH("finalize_mean_peers launch");
     return IVX_OK;
 }
