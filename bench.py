@@ -353,7 +353,8 @@ def gpu_reference(sc, batch, P, origin, workload, dev):
     return out
 
 
-def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev, peaks, scenes_per_rank=None):
+def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev, peaks, scenes_per_rank=None,
+                        view_group=None):
     """Strong scaling of one multi-view configuration: the V views of every scene of ONE fixed batch are
     sharded over the `world` ranks (rank r takes views r, r + world, ...), every rank back-projects its
     views into partial sums / counts in symmetric memory, `ivx_finalize_mean_peers` reduces them over
@@ -362,9 +363,18 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
     on the device (seeded per view, identical on every rank); K steps are replayed from one CUDA graph.
     `scenes_per_rank` (throughput mode): the step holds scenes_per_rank * world scenes, so
     that after the scatter every rank runs its neck on a full batch; compare with the one-GPU record
-    through scenes_per_s."""
+    through scenes_per_s.
+    `view_group` = (process group, ways): hybrid of the two axes -- the ranks form world / ways groups, the views
+    of a scene are sharded over the `ways` ranks of one group only (its own symmetric-memory buffers and
+    barriers) and every group works on its own scenes, so the NVLink exchange per GPU shrinks from
+    (world - 1) / world to (ways - 1) / ways of the partial volumes while all `world` GPUs stay busy."""
     from imvoxelnet_b200 import necks, ops, sharding
     sc, batch, P, origin = scene_setup(name)
+    n_groups, group_index, pg, all_ranks = 1, 0, None, world
+    if view_group is not None:
+        pg, ways = view_group
+        n_groups, group_index = world // ways, rank // ways
+        world, rank = ways, rank % ways            # from here on: position inside the view group
     if scenes_per_rank is not None:
         batch = scenes_per_rank * world
     V, C, N = sc.n_views, sc.channels, sc.n_total_voxels
@@ -376,7 +386,7 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
 
     def view_features(v, scene_slice=slice(None)):      # [b, hf, wf, C]: channels-last maps of view v
         g = torch.Generator(device=dev)
-        g.manual_seed(1234 + v)
+        g.manual_seed(1234 + v + 1000 * group_index)
         return torch.randn((batch, hf, wf, C), generator=g, device=dev)[scene_slice]
 
     def stack(views, scene_slice=slice(None)):          # logical [b, V', C, hf, wf], NHWC memory
@@ -396,7 +406,7 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
         use_mc = collective == "multimem" or (collective == "auto" and world > 2)
         # two sets of partial-sum buffers ("lanes"): consecutive steps alternate between them, so the
         # exchange of one step can overlap the neck of the step before it (pipelined timing below)
-        lanes = [sharding.FusedViewSharded(batch, C, sc.n_voxels, use_multicast=use_mc) for _ in range(2)]
+        lanes = [sharding.FusedViewSharded(batch, C, sc.n_voxels, group=pg, use_multicast=use_mc) for _ in range(2)]
         fused = lanes[0]
 
     def backproject(out_dtype, lane=0):
@@ -445,19 +455,21 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
         return statistics.median(totals), graph
 
     def barrier():
-        if world > 1:
+        if all_ranks > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    rec = {"workload": sc.name, "scenes_per_step": batch, "views": V, "n_gpus": world,
+    rec = {"workload": sc.name, "scenes_per_step": batch * n_groups, "views": V, "n_gpus": all_ranks,
+           "view_sharding_ways": world, "scene_groups": n_groups,
            "mode": ("strong scaling: one fixed batch" if scenes_per_rank is None else
-                    f"throughput: {scenes_per_rank} scenes per rank in flight, views still sharded"),
+                    f"throughput: {scenes_per_rank} scenes per rank in flight, views sharded {world}-way"
+                    + (f" inside each of {n_groups} groups of GPUs" if n_groups > 1 else "")),
            "views_on_rank0": len(my_views), "scenes_finalized_on_rank0": my_scenes, "neck": cls + " (bf16)"}
     with torch.no_grad():
         # self-check on rank 0 (all ranks take part in the collective): the sharded fp32 volume of its
         # scenes against the unsharded kernel on all V views of the same scenes
         vol32, valid, count = backproject(torch.float32)
-        if world > 1 and rank == 0 and my_scenes > 0:
+        if world > 1 and rank == 0 and group_index == 0 and my_scenes > 0:
             full = stack(list(range(V)), mine)
             pf = P.unsqueeze(0).expand(my_scenes, V, 3, 4).contiguous().to(dev)
             ref, ref_valid, ref_count = ops.backproject_scenes(full, hws[:my_scenes], pf, sc.n_voxels, sc.voxel_size,
@@ -495,13 +507,14 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
             bp_total, total = res
     t = torch.tensor([total, bp_total, pipelined_total if pipelined_total is not None else -1.0], device=dev,
                      dtype=torch.float64)
-    if world > 1:
+    if all_ranks > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total, bp_total, pipelined_total = (float(v) for v in t.tolist())
     ms, bp_ms = total / steps, bp_total / steps
+    batch_all = batch * n_groups
     if pipelined_total > 0:
         rec["pipelined"] = {"ms_per_step": pipelined_total / steps,
-                            "scenes_per_s": batch / (pipelined_total / steps * 1e-3),
+                            "scenes_per_s": batch_all / (pipelined_total / steps * 1e-3),
                             "what": "the same K steps, consecutive steps on two streams with two sets of "
                                     "partial-sum buffers: a step's NVLink reduction overlaps the previous step's neck"}
     neck_ms = max(ms - bp_ms, 1e-6)
@@ -511,7 +524,7 @@ def view_sharded_record(name, steps, warmup, collective, dist, world, rank, dev,
     partial_bytes = batch * N * (C + 1) * 4                          # what every rank writes
     nvlink_in = per_rank * N * (C + 1) * 4 * (world - 1)              # peers' partials of this rank's scenes
     rec.update({
-        "ms_per_step": ms, "scenes_per_s": batch / (ms * 1e-3), "voxel_views_per_s": batch * V * N / (ms * 1e-3),
+        "ms_per_step": ms, "scenes_per_s": batch_all / (ms * 1e-3), "voxel_views_per_s": batch_all * V * N / (ms * 1e-3),
         "timing": mode,
         "stages": {"backproject_reduce_finalize_ms": bp_ms, "neck_ms": neck_ms},
         "collective": ("none (one GPU)" if fused is None else
@@ -832,6 +845,12 @@ def run_ours(args):
                     extras["view_sharded"].append(view_sharded_record(
                         "scannet_fast", args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks,
                         scenes_per_rank=WORKLOADS["scannet_fast"][1]))
+                if world >= 4 and world % 2 == 0:
+                    # hybrid: pairs of GPUs share the views of their scenes, the pairs are data-parallel
+                    groups = [dist.new_group(list(range(g * 2, g * 2 + 2))) for g in range(world // 2)]
+                    extras["view_sharded"].append(view_sharded_record(
+                        "scannet_fast", args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks,
+                        scenes_per_rank=WORKLOADS["scannet_fast"][1], view_group=(groups[rank // 2], 2)))
 
     if rank == 0:
         cpu = None

@@ -1,14 +1,15 @@
 #!/bin/bash
-# Run bench.py on every workload and print a one-line digest of each (GPU box).
-for w in kitti scannet_fast sunrgbd_fast nuscenes nuscenes_refgrid total_sunrgbd; do
-  python bench.py --workload $w "$@" > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err || { echo "$w FAILED"; tail -5 gpurun_out/bench_$w.err; continue; }
+# Every single-GPU workload of bench.py, one JSON line each into gpurun_out/bench_<workload>.json (GPU box).
+cd "${GRAFT_REPO_ROOT:-$(dirname "$0")/..}"
+mkdir -p gpurun_out
+for w in kitti scannet_fast sunrgbd_fast total_sunrgbd nuscenes nuscenes_refgrid; do
+  extra="--no-extras"; [ "$w" = kitti ] && extra=""
+  timeout 600 python bench.py --workload $w --steps 20 --warmup 5 $extra > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err
+  echo "$w rc=$?"
   python - <<PY
 import json
-d=json.load(open("gpurun_out/bench_$w.json"))
-r=d["roofline_backproject"]; st=d["stages"]
-nk=st.get("neck")
-print("$w", "step %.3f ms"%d["ms_per_step"], "| bp %.4f ms %.0f GB/s frac %.3f"%(st["backproject"]["ms"], r["achieved"], r["frac"]),
-      "| neck " + ("%.2f ms %.0f TF/s frac %.3f"%(nk["ms"], nk["tflops"], d["roofline"]["frac"]) if nk else "-"),
-      "| scenes/s %.0f e2e %.0f cpu %.3g"%(d["scenes_per_s"], d["e2e"]["scenes_per_s"], d["cpu_baseline"]["scenes_per_s"]), d["clocks"]["sm_mhz"], d["clocks"]["reasons"])
+d=json.loads(open('gpurun_out/bench_$w.json').read().strip().splitlines()[-1])
+r=d.get('roofline') or {}; rb=d.get('roofline_backproject') or {}
+print('  step %.3f ms, bp %.4f ms frac %.3f, neck frac %s, e2e %.3f ms, scenes/s %.0f, cpu %s' % (d['ms_per_step'], rb.get('kernel_ms',0), rb.get('frac',0), round(r.get('frac',0),3) if r.get('bound')=='tensor' else None, d['e2e']['ms_per_step'], d['scenes_per_s'], (d.get('cpu_baseline') or {}).get('scenes_per_s')))
 PY
 done
