@@ -847,10 +847,10 @@ def run_ours(args):
                         scenes_per_rank=WORKLOADS["scannet_fast"][1]))
                 if world >= 4 and world % 2 == 0:
                     # hybrid: pairs of GPUs share the views of their scenes, the pairs are data-parallel
-                    groups = [dist.new_group(list(range(g * 2, g * 2 + 2))) for g in range(world // 2)]
+                    pair, _, _ = sharding.view_groups(2, world, rank)
                     extras["view_sharded"].append(view_sharded_record(
                         "scannet_fast", args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks,
-                        scenes_per_rank=WORKLOADS["scannet_fast"][1], view_group=(groups[rank // 2], 2)))
+                        scenes_per_rank=WORKLOADS["scannet_fast"][1], view_group=(pair, 2)))
 
     if rank == 0:
         cpu = None

@@ -71,3 +71,40 @@ def test_view_sharded_sum_over_gloo(tmp_path):
     mean = np.where(cnt > 0, got["s"] / np.maximum(cnt, 1), 0).astype(np.float32)
     assert_volume_close(mean, ref)
     assert np.array_equal(cnt > 0, ref_valid[0])
+
+
+def _group_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        group, gi, lr = sharding.view_groups(2)
+        assert (gi, lr) == (rank // 2, rank % 2) and dist.get_world_size(group) == 2
+        sc, full, P, pts = _scene()
+        full = full + gi                                   # every group has its own scene
+        mine = sharding.shard_views(sc.n_views, lr, 2)
+        vol, valid = ob.backproject(full[mine], pts, P[mine])
+        s = torch.from_numpy(vol.sum(0))
+        c = torch.from_numpy(valid.sum(0)[0].astype(np.int32))
+        sharding.allreduce_partials(s, c, group)           # only inside the pair
+        if lr == 0:
+            np.savez(out % gi, s=s.numpy(), c=c.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_view_groups_reduce_inside_each_group_only(tmp_path):
+    """4 gloo ranks = 2 pairs: the views of a scene are sharded over one pair, the pairs hold different scenes."""
+    out = str(tmp_path / "group%d.npz")
+    port = 31500 + os.getpid() % 2000
+    mp.spawn(_group_worker, args=(4, port, out), nprocs=4, join=True)
+    sc, full, P, pts = _scene()
+    for gi in range(2):
+        got = np.load(out % gi)
+        ref, ref_valid, ref_cnt = ob.backproject_mean(full + gi, pts, P)
+        assert np.array_equal(got["c"], ref_cnt)
+        cnt = got["c"].astype(np.float32)
+        mean = np.where(cnt > 0, got["s"] / np.maximum(cnt, 1), 0).astype(np.float32)
+        assert_volume_close(mean, ref)
+    with pytest.raises(ValueError):
+        sharding.view_groups(3, world_size=8, rank=0)
