@@ -298,3 +298,21 @@ def test_train_mode_without_grad_uses_batch_statistics():
     for k in a:
         if "running_mean" in k or "running_var" in k:
             assert_volume_close(a[k].cpu().numpy(), b[k].cpu().numpy(), rel=5e-5)
+
+
+def test_x3_neck_on_a_batch_matches_the_cuda_core_path():
+    """The 3xTF32 tensor-core path against the CUDA-core kernel on a batch of four KITTI-grid scenes:
+    persistent CTAs loop over ~80 tiles each and every tile sums many accumulation periods."""
+    kw = FULL["KittiImVoxelNeck"][0]
+    torch.manual_seed(12)
+    m = necks.KittiImVoxelNeck(**kw).eval()
+    torch_necks.randomize_norms(m, 7)
+    m.to(DEV)
+    x = torch.randn(4, 64, 216, 248, 12, device=DEV).contiguous(memory_format=torch.channels_last_3d)
+    with torch.no_grad():
+        m.precision = "fp32"
+        got = m(x)[0]
+        m.precision = "fp32_simt"
+        want = m(x)[0]
+    assert rel_l2(got, want) <= 1e-5
+    assert_volume_close(got.cpu().numpy(), want.cpu().numpy())
