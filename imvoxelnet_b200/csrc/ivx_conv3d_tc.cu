@@ -858,6 +858,24 @@ extern "C" int ivx_conv3d_ndhwc_tf32_tc_view(const ivx_conv3d_params *p, const f
                            y_strides);
 }
 
+extern "C" int ivx_conv3d_ndhwc_f32x3_tc_view(const ivx_conv3d_params *p, const float *x_split,
+                                              const float *weight_split, const float *scale, const float *shift,
+                                              float *y, const int64_t *y_strides, void *workspace,
+                                              int64_t workspace_bytes, void *stream) {
+    IVX_REQUIRE(p && x_split && weight_split && y && y_strides, "NULL argument");
+    int rc0 = validate_tc(p, false, true);
+    if (rc0 != IVX_OK) return rc0;
+    IVX_REQUIRE(p->in_dtype == IVX_F32X2 && p->out_dtype == IVX_F32 && !p->transposed,
+                "plain convolutions of split fp32 activations (IVX_F32X2) only");
+    IVX_REQUIRE((reinterpret_cast<uintptr_t>(x_split) | reinterpret_cast<uintptr_t>(y) |
+                 reinterpret_cast<uintptr_t>(weight_split)) % 16 == 0,
+                "tensors must be 16-byte aligned");
+    for (int i = 0; i < 4; ++i)
+        IVX_REQUIRE(y_strides[i] > 0 && y_strides[i] % 4 == 0, "output strides must be positive multiples of 4 elements");
+    return launch_tc<true, true>(p, x_split, weight_split, scale, shift, nullptr, y, workspace, workspace_bytes,
+                                 (cudaStream_t)stream, y_strides);
+}
+
 extern "C" int ivx_conv3d_ndhwc_f32x3_tc(const ivx_conv3d_params *p, const float *x_split, const float *weight_split,
                                          const float *scale, const float *shift, const float *residual, float *y,
                                          void *workspace, int64_t workspace_bytes, void *stream) {

@@ -61,6 +61,32 @@ def _tf32_ok(c_in, c_out):
     return conv._TF32 and c_in % 32 == 0 and c_out % 64 == 0
 
 
+def _x3_ok(c_in, c_out):
+    """fp32 training: convolutions of eligible layers (forward, stride-1 and transposed data gradients) as
+    three tf32 products on the tensor cores (3xTF32, 1e-5 of fp32), like the inference path."""
+    from . import conv
+    return conv._FP32X3 and not conv._TF32 and c_in % 32 == 0 and c_out % 64 == 0
+
+
+def _tc_ok(c_in, c_out):
+    return _tf32_ok(c_in, c_out) or _x3_ok(c_in, c_out)
+
+
+def _conv_tc(fc, params, x, w_tc, bias, y):
+    """y = conv(x) + bias on the tensor cores: tf32 math under precision "tf32", else 3xTF32 (fp32 grade)."""
+    from . import conv
+    if conv._TF32:
+        return _conv_tf32(fc, params, x, w_tc, bias, y)
+    q = _copy_params(params, in_dtype=_lib.IVX_F32X2)
+    rows = w_tc.reshape(-1, w_tc.shape[-1]) if params.transposed else w_tc.reshape(w_tc.shape[0], -1)
+    hi = conv._rna_tf32(rows)
+    w_split = torch.stack([hi, conv._rna_tf32(rows - hi)], dim=1).contiguous()
+    xs = conv.split_tf32(x.contiguous())
+    ws = fc._workspace(q, x.device)
+    _call("ivx_conv3d_ndhwc_f32x3_tc", q, xs.data_ptr(), w_split.data_ptr(), None, _ptr(bias), None, y.data_ptr(),
+          ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
+
+
 def _conv_tf32(fc, params, x, w_tc, bias, y):
     """y = conv(x) + bias on the tensor cores with tf32 math (weights in the tensor-core layout)."""
     ws = fc._workspace(params, x.device)
@@ -154,6 +180,9 @@ def _dgrad_strided_tf32(fc, p, dz, wp, dx):
     full = all(ph is not None for per in plans for ph in per)
     if not full:
         dx.zero_()                  # phases no tap reaches keep a zero gradient
+    from . import conv as _conv
+    x3 = not _conv._TF32            # fp32 training: the same phases with three tf32 products (3xTF32)
+    dz_in = _conv.split_tf32(dz.contiguous()) if x3 else dz
     n_taps = k3[0] * k3[1] * k3[2]
     # the layer's taps as rows, plus one zero row for the holes of a phase's sub-kernel
     taps_ext = torch.cat((wp.reshape(n_taps, cin, cout), wp.new_zeros((1, cin, cout))))
@@ -177,9 +206,16 @@ def _dgrad_strided_tf32(fc, p, dz, wp, dx):
                 q = _copy_params(p, c_in=cout, c_out=cin, in_dims=out_dims, out_dims=view_dims,
                                  kernel=tuple(len(x) for x in sel), stride=(1, 1, 1), pad=(ph0[1], ph1[1], ph2[1]),
                                  relu=0, residual_after_act=0, post_scale=1.0)
+                entry = "ivx_conv3d_ndhwc_tf32_tc_view"
+                if x3:
+                    q.in_dtype = _lib.IVX_F32X2
+                    rows = w.reshape(cin, -1)
+                    hi = _conv._rna_tf32(rows)
+                    w = torch.stack([hi, _conv._rna_tf32(rows - hi)], dim=1).contiguous()
+                    entry = "ivx_conv3d_ndhwc_f32x3_tc_view"
                 ws = fc._workspace(q, dz.device)
                 base = dx.data_ptr() + 4 * (r0 * sx + r1 * sy + r2 * sz)
-                _call("ivx_conv3d_ndhwc_tf32_tc_view", q, dz.data_ptr(), w.data_ptr(), None, None, base,
+                _call(entry, q, dz_in.data_ptr(), w.data_ptr(), None, None, base,
                       _lib.i64([s3[0] * sx, s3[1] * sy, s3[2] * sz, sb]),
                       ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0)
     return True
@@ -210,9 +246,9 @@ class _FusedLayer(torch.autograd.Function):
         wp = (w.permute(0, 2, 3, 4, 1) if fc.transposed else w.permute(2, 3, 4, 1, 0)).contiguous()
         z = torch.empty((b,) + od + (cout,), dtype=torch.float32, device=dev)
         bias_f = bias.detach().float().contiguous() if bias is not None else None
-        if _tf32_ok(cin, cout):      # precision "tf32": the convolution itself on the tensor cores
+        if _tc_ok(cin, cout):        # the convolution itself on the tensor cores ("tf32": tf32 math; "fp32": 3xTF32)
             w_tc = (w.permute(2, 3, 4, 1, 0) if fc.transposed else w.permute(0, 2, 3, 4, 1)).contiguous()
-            _conv_tf32(fc, p, x, w_tc, bias_f, z)
+            _conv_tc(fc, p, x, w_tc, bias_f, z)
         else:
             _call("ivx_conv3d_ndhwc", p, x.data_ptr(), wp.data_ptr(), None, _ptr(bias_f), None, z.data_ptr())
         rows = z.numel() // cout
@@ -244,6 +280,7 @@ class _FusedLayer(torch.autograd.Function):
                   int(after), float(post), rows, cout, y.data_ptr())
         from . import conv as _conv
         ctx.tf32 = _conv._TF32       # the backward pass runs outside the neck's tf32 context: remember it
+        ctx.x3 = _conv._FP32X3
         ctx.fc, ctx.p, ctx.flags = fc, p, (after, post, trivial, batch_stats, rows)
         ctx.has_bias = bias is not None
         keep_res = residual if (residual is not None and fc.relu and not after) else None
@@ -254,7 +291,7 @@ class _FusedLayer(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy):
         from . import conv as _conv
-        with _conv.tf32(ctx.tf32):
+        with _conv.tf32(ctx.tf32), _conv.fp32x3(ctx.x3):
             return _FusedLayer._backward(ctx, dy)
 
     @staticmethod
@@ -302,19 +339,19 @@ class _FusedLayer(torch.autograd.Function):
             if fc.transposed:    # data gradient of a kernel == stride transposed conv: a plain strided conv of dz
                 q = _copy_params(p, c_in=cout, c_out=cin, in_dims=tuple(p.out_dims), out_dims=tuple(p.in_dims),
                                  transposed=0, relu=0, residual_after_act=0, post_scale=1.0)
-                if _tf32_ok(cout, cin):
-                    _conv_tf32(fc, q, dz, wp.contiguous(), None, dx)   # wp is [Cin][k][k][k][Cout] already
+                if _tc_ok(cout, cin):
+                    _conv_tc(fc, q, dz, wp.contiguous(), None, dx)   # wp is [Cin][k][k][k][Cout] already
                 else:
                     wt = wp.permute(1, 2, 3, 4, 0).contiguous()    # [Cin,k,k,k,Cout] -> [taps][Cout][Cin]
                     _call("ivx_conv3d_ndhwc", q, dz.data_ptr(), wt.data_ptr(), None, None, None, dx.data_ptr())
-            elif unit_stride and _tf32_ok(cout, cin):
+            elif unit_stride and _tc_ok(cout, cin):
                 # stride 1: the data gradient is the convolution of dz with the flipped, transposed kernel
                 q = _copy_params(p, c_in=cout, c_out=cin, in_dims=tuple(p.out_dims), out_dims=tuple(p.in_dims),
                                  pad=tuple(p.kernel[d] - 1 - p.pad[d] for d in range(3)), relu=0,
                                  residual_after_act=0, post_scale=1.0)
                 w_flip = wp.flip(0, 1, 2).permute(3, 0, 1, 2, 4).contiguous()   # [k][k][k][Cin][Cout] -> [Cin][k'][Cout]
-                _conv_tf32(fc, q, dz, w_flip, None, dx)
-            elif _tf32_ok(cout, cin) and _dgrad_strided_tf32(fc, p, dz, wp, dx):
+                _conv_tc(fc, q, dz, w_flip, None, dx)
+            elif _tc_ok(cout, cin) and _dgrad_strided_tf32(fc, p, dz, wp, dx):
                 pass                                               # strided layer: one tensor-core launch per phase
             else:
                 wt = wp.permute(0, 1, 2, 4, 3).contiguous()        # [taps][Cin][Cout] -> [taps][Cout][Cin]

@@ -417,6 +417,12 @@ IVX_API int ivx_conv3d_ndhwc_f32x3_tc(const ivx_conv3d_params *params, const flo
                                       const float *residual, float *y, void *workspace,
                                       int64_t workspace_bytes, void *stream);
 IVX_API int ivx_split_tf32_ndhwc(const float *x, float *y, int64_t rows, int n_channels, void *stream);
+/* ivx_conv3d_ndhwc_tf32_tc_view (below) in the 3xTF32 mode: fp32-grade data gradients of strided layers,
+ * one input phase per call, written into a strided view of the gradient (training in fp32). */
+IVX_API int ivx_conv3d_ndhwc_f32x3_tc_view(const ivx_conv3d_params *params, const float *x_split,
+                                           const float *weight_split, const float *scale, const float *shift,
+                                           float *y, const int64_t *y_strides /* host[4] */, void *workspace,
+                                           int64_t workspace_bytes, void *stream);
 
 /*
  * ivx_upsample2x_trilinear_ndhwc -- F.interpolate(x, scale_factor=2,
