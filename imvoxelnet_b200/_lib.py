@@ -91,6 +91,7 @@ PROTOTYPES["ivx_head_scores"] = [c_void_p, c_void_p, c_void_p, c_int, c_int64, c
 PROTOTYPES["ivx_compute_projection"] = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p]
 PROTOTYPES["ivx_conv3d_wgrad_tf32_axes"] = [_ConvP, _i32p]
 PROTOTYPES["ivx_conv3d_wgrad_tf32_tc"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p]
+PROTOTYPES["ivx_conv3d_wgrad_f32x3_tc"] = PROTOTYPES["ivx_conv3d_wgrad_tf32_tc"]
 PROTOTYPES["ivx_conv3d_ndhwc_tf32_tc_view"] = [_ConvP, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, _i64p,
                                                c_void_p, c_int64, c_void_p]
 PROTOTYPES["ivx_conv3d_ndhwc_f32x3_tc_view"] = PROTOTYPES["ivx_conv3d_ndhwc_tf32_tc_view"]

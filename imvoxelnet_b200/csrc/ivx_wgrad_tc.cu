@@ -41,6 +41,10 @@ struct WgArgs {
     int orig_kernel[3];              // kernel sizes along X, Y, Z
     int box[3], chunks[3], batch;    // voxels per k-step along each permuted axis, k-steps per axis
     long long k_steps;               // batch * chunks[0] * chunks[1] * chunks[2]
+    // 3xTF32 (fp32-grade gradients, see ivx_conv3d_tc_halo.cu): both operands carry 2 C channels (hi | lo) and
+    // the k-steps run three passes over the voxels: (x_lo, dz_hi), (x_hi, dz_lo), (x_hi, dz_hi)
+    int x3;
+    long long k_total;               // k_steps, or 3 * k_steps (x3)
     int k_splits;
     long long steps_per_split;
     int stages;
@@ -93,12 +97,16 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
     const int t1_lo = a.group > 1 ? 0 : (tap_g / a.kernel[0]) % a.kernel[1];
     const int t2 = a.group > 1 ? tap_g / a.kernel[0] : tap_g / (a.kernel[0] * a.kernel[1]);
     const long long k_lo = (long long)split * a.steps_per_split;
-    const long long k_hi = k_lo + a.steps_per_split < a.k_steps ? k_lo + a.steps_per_split : a.k_steps;
+    const long long k_hi = k_lo + a.steps_per_split < a.k_total ? k_lo + a.steps_per_split : a.k_total;
 
     if (warp == 0) {
         if (lane == 0) {
             uint32_t stage = 0, phase = 0;
-            for (long long ks = k_lo; ks < k_hi; ++ks) {
+            for (long long ks0 = k_lo; ks0 < k_hi; ++ks0) {
+                const int pass = a.x3 ? (int)(ks0 / a.k_steps) : 2;
+                const long long ks = ks0 - (a.x3 ? pass * a.k_steps : 0);
+                const int dz_ch = (a.x3 && pass == 1) ? a.c_out : 0;      // lo half of grad_z
+                const int x_ch = (a.x3 && pass == 0) ? a.c_in : 0;        // lo half of x
                 int r0, r1, r2;
                 int t = a.div_c0.divmod((int)ks, r0);
                 t = a.div_c1.divmod(t, r1);
@@ -113,10 +121,10 @@ conv3d_wgrad_tc_kernel(const __grid_constant__ CUtensorMap map_dz, const __grid_
                     // a box always arrives in full, whatever part of it lies outside the tensor
                     mbar_expect_tx(bar, (uint32_t)(((a.debug & 8) ? 0 : a.a_rows * 128) +
                                                    ((a.debug & 16) ? 0 : a.group * b_bytes)));
-                    if (!(a.debug & 8)) tma_load_5d(sa, &map_dz, bar, 0, co_t * 128, r0, o1, b * a.dz_planes + o2);
+                    if (!(a.debug & 8)) tma_load_5d(sa, &map_dz, bar, 0, dz_ch + co_t * 128, r0, o1, b * a.dz_planes + o2);
                     if (!(a.debug & 16))
                         for (int g = 0; g < a.group; ++g)
-                            tma_load_5d(sa + WG_A_BYTES + g * b_bytes, &map_x, bar, 0, ci_t * a.n_tile, r0,
+                            tma_load_5d(sa + WG_A_BYTES + g * b_bytes, &map_x, bar, 0, x_ch + ci_t * a.n_tile, r0,
                                         o1 * a.stride[1] - a.pad[1] + t1_lo + g,
                                         (t0 * a.batch + b) * a.x_planes + o2 * a.stride[2] + t2);
                 }
@@ -218,8 +226,21 @@ extern "C" int ivx_conv3d_wgrad_tf32_axes(const ivx_conv3d_params *p, int32_t *a
     return IVX_OK;
 }
 
+static int launch_wgrad(const ivx_conv3d_params *p, const float *x_t, const float *dz_t, float *grad_w, void *stream,
+                        bool x3);
+
 extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float *x_t, const float *dz_t,
                                         float *grad_w, void *stream) {
+    return launch_wgrad(p, x_t, dz_t, grad_w, stream, false);
+}
+
+extern "C" int ivx_conv3d_wgrad_f32x3_tc(const ivx_conv3d_params *p, const float *x_t_split, const float *dz_t_split,
+                                         float *grad_w, void *stream) {
+    return launch_wgrad(p, x_t_split, dz_t_split, grad_w, stream, true);
+}
+
+static int launch_wgrad(const ivx_conv3d_params *p, const float *x_t, const float *dz_t, float *grad_w, void *stream,
+                        bool x3) {
     IVX_REQUIRE(p && x_t && dz_t && grad_w, "NULL argument");
     int32_t axes[3];
     int rc = ivx_conv3d_wgrad_tf32_axes(p, axes);
@@ -249,16 +270,20 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
         a.chunks[i] = (p->out_dims[axis[i]] + a.box[i] - 1) / a.box[i];
         k_steps *= a.chunks[i];
     }
-    IVX_REQUIRE(k_steps < (1ll << 31), "too many voxels");
+    IVX_REQUIRE(k_steps < (1ll << 31) / 3, "too many voxels");
     a.k_steps = k_steps;
+    a.x3 = x3 ? 1 : 0;
+    a.k_total = x3 ? 3 * k_steps : k_steps;
+    const long long k_all = a.k_total;
+    const int ch_mul = x3 ? 2 : 1;          // channels per voxel in the operand copies: (hi | lo)
     const int n_taps = p->kernel[0] * p->kernel[1] * p->kernel[2];
     const long long tiles = (long long)(n_taps / a.group) * a.co_tiles * a.ci_tiles;
     // enough k-slices to fill the GPU a few times over, at least 64 k-steps each
     long long splits = (4ll * kNumSMs + tiles - 1) / tiles;
-    if (splits > k_steps / 64) splits = k_steps / 64;
+    if (splits > k_all / 64) splits = k_all / 64;
     if (splits < 1) splits = 1;
-    a.steps_per_split = (k_steps + splits - 1) / splits;
-    a.k_splits = (int)((k_steps + a.steps_per_split - 1) / a.steps_per_split);
+    a.steps_per_split = (k_all + splits - 1) / splits;
+    a.k_splits = (int)((k_all + a.steps_per_split - 1) / a.steps_per_split);
     IVX_REQUIRE(tiles * a.k_splits < (1ll << 31), "too many work items");
     a.dw = grad_w;
     a.a_rows = p->c_out < 128 ? p->c_out : 128;
@@ -280,18 +305,18 @@ extern "C" int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *p, const float 
     const cuuint32_t es[5] = {1, 1, 1, 1, 1};
     alignas(64) CUtensorMap map_dz, map_x;
     {   // (voxel in run, channel, run along D0, D1, plane x batch)
-        const cuuint64_t dims[5] = {32, (cuuint64_t)p->c_out, n_runs, (cuuint64_t)p->out_dims[axis[1]],
+        const cuuint64_t dims[5] = {32, (cuuint64_t)p->c_out * ch_mul, n_runs, (cuuint64_t)p->out_dims[axis[1]],
                                     (cuuint64_t)a.dz_planes * p->batch};
-        cuuint64_t st[4] = {128, (cuuint64_t)p->c_out * 128, 0, 0};
+        cuuint64_t st[4] = {128, (cuuint64_t)p->c_out * ch_mul * 128, 0, 0};
         st[2] = st[1] * n_runs, st[3] = st[2] * p->out_dims[axis[1]];
         const cuuint32_t box[5] = {32, (cuuint32_t)a.a_rows, 1, 1, 1};
         rc = encode_map_sw128(&map_dz, dt, 5, const_cast<float *>(dz_t), dims, st, box, es, "grad_z (tiled channel-major)");
         if (rc != IVX_OK) return rc;
     }
     {   // the same for x, with one copy per tap position along D0 and the zero planes along D2
-        const cuuint64_t dims[5] = {32, (cuuint64_t)p->c_in, n_runs, (cuuint64_t)p->in_dims[axis[1]],
+        const cuuint64_t dims[5] = {32, (cuuint64_t)p->c_in * ch_mul, n_runs, (cuuint64_t)p->in_dims[axis[1]],
                                     (cuuint64_t)a.x_planes * p->batch * p->kernel[axis[0]]};
-        cuuint64_t st[4] = {128, (cuuint64_t)p->c_in * 128, 0, 0};
+        cuuint64_t st[4] = {128, (cuuint64_t)p->c_in * ch_mul * 128, 0, 0};
         st[2] = st[1] * n_runs, st[3] = st[2] * p->in_dims[axis[1]];
         const cuuint32_t box[5] = {32, (cuuint32_t)a.n_tile, 1, 1, 1};
         rc = encode_map_sw128(&map_x, dt, 5, const_cast<float *>(x_t), dims, st, box, es, "x (tiled channel-major)");

@@ -114,7 +114,8 @@ def _channel_major(t, axes, shifts=None, out_len=None, step=1, halo=0):
 def _wgrad_tf32(p, x, dz):
     """Weight gradient on the tensor cores in torch's layout, or None when the layer is not one it takes."""
     from . import conv
-    if not conv._TF32 or p.c_in % 32 or p.c_out % 32:
+    x3 = not conv._TF32 and conv._FP32X3        # fp32 training: three tf32 products over split operands
+    if not (conv._TF32 or x3) or p.c_in % 32 or p.c_out % 32:
         return None
     if p.transposed:
         # y[s*i + t] += x[i] * w[ci, co, t]: the plain convolution from the OUTPUT grid (channels c_out) to
@@ -133,6 +134,8 @@ def _wgrad_tf32(p, x, dz):
     if PROFILE is not None:
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
+    if x3:      # (hi | lo) halves of both operands: 2 C channels each from here on
+        src, grad = conv.split_tf32(src.contiguous()), conv.split_tf32(grad.contiguous())
     x_t = _channel_major(src, axes, shifts=[j - q.pad[a0] for j in range(q.kernel[a0])],
                          out_len=q.out_dims[a0], step=q.stride[a0], halo=q.pad[axes[2]])
     dz_t = _channel_major(grad, axes)
@@ -144,7 +147,8 @@ def _wgrad_tf32(p, x, dz):
         rec[1] += e0.elapsed_time(e1)
     k = tuple(q.kernel)
     dw = torch.zeros((k[0], k[1], k[2], q.c_out, q.c_in), dtype=torch.float32, device=x.device)
-    _call("ivx_conv3d_wgrad_tf32_tc", q, x_t.data_ptr(), dz_t.data_ptr(), dw.data_ptr())
+    _call("ivx_conv3d_wgrad_f32x3_tc" if x3 else "ivx_conv3d_wgrad_tf32_tc", q, x_t.data_ptr(), dz_t.data_ptr(),
+          dw.data_ptr())
     if p.transposed:
         return dw.permute(3, 4, 0, 1, 2)    # [k][k][k][Cin_T][Cout_T] -> torch's [Cin_T, Cout_T, kX, kY, kZ]
     return dw.permute(3, 4, 0, 1, 2)        # torch's [Cout, Cin, kX, kY, kZ]

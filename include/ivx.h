@@ -534,6 +534,11 @@ IVX_API int ivx_conv3d_wgrad_tf32_tc(const ivx_conv3d_params *params, const floa
 
 /* grad_x [batch][X][Y][Z][C] += transpose of ivx_upsample2x_trilinear_ndhwc applied to grad_y
  * [batch][2X][2Y][2Z][C]; grad_x must be zero-filled by the caller */
+/* ivx_conv3d_wgrad_tf32_tc at fp32 grade (3xTF32): x_t / dz_t are the tiled channel-major copies
+ * (ivx_channel_major_ndhwc with 2 * C channels) of the SPLIT tensors written by ivx_split_tf32_ndhwc;
+ * params carry the layer's own c_in / c_out.  Used by fp32 training. */
+IVX_API int ivx_conv3d_wgrad_f32x3_tc(const ivx_conv3d_params *params, const float *x_t_split,
+                                      const float *dz_t_split, float *grad_w, void *stream);
 IVX_API int ivx_upsample2x_trilinear_backward_ndhwc(const float *grad_y, float *grad_x, int batch,
                                                     int n_channels, const int32_t *in_dims /* host[3] */,
                                                     void *stream);
