@@ -888,6 +888,15 @@ def run_ours(args):
                   "on side streams"}
 
     extras = {}
+
+    def guarded(fn, *a, **k):
+        """A side record must never take the headline line down with it."""
+        try:
+            return fn(*a, **k)
+        except Exception as exc:          # e.g. no symmetric memory on this machine
+            torch.cuda.synchronize()
+            return {"error": f"{type(exc).__name__}: {exc}"[:300]}
+
     if not args.no_extras:
         with torch.no_grad():
             if neck is not None and args.neck_precision == "bf16" and not view_sharded:
@@ -908,25 +917,24 @@ def run_ours(args):
                                               "(tf32 : bf16) / 3 (tf32 products per fp32-grade product)",
                                  "kernel": "conv3d_tc_halo_kernel<tf32, x3> / conv3d_tc_kernel<tf32, x3> + split_tf32_kernel"}}
             if world == 1:
-                extras["gpu_reference"] = gpu_reference(sc, batch, P, origin, args.workload, dev)
+                extras["gpu_reference"] = guarded(gpu_reference, sc, batch, P, origin, args.workload, dev)
             if not view_sharded:
                 del dev_sets
                 torch.cuda.empty_cache()
-                extras["view_sharded"] = [
-                    view_sharded_record(name, args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks)
-                    for name in ("scannet_fast", "nuscenes_refgrid")]
+                common = (args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks)
+                extras["view_sharded"] = [guarded(view_sharded_record, name, *common)
+                                          for name in ("scannet_fast", "nuscenes_refgrid")]
                 if world > 1:
-                    extras["view_sharded"].append(view_sharded_record(
-                        "scannet_fast", args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks,
-                        scenes_per_rank=WORKLOADS["scannet_fast"][1]))
-                extras["detector_view_sharded"] = detector_record(args.steps, args.warmup, args.collective, dist,
-                                                                  world, rank, dev)
+                    extras["view_sharded"].append(guarded(view_sharded_record, "scannet_fast", *common,
+                                                          scenes_per_rank=WORKLOADS["scannet_fast"][1]))
+                extras["detector_view_sharded"] = guarded(detector_record, args.steps, args.warmup, args.collective,
+                                                          dist, world, rank, dev)
                 if world >= 4 and world % 2 == 0:
                     # hybrid: pairs of GPUs share the views of their scenes, the pairs are data-parallel
                     pair, _, _ = sharding.view_groups(2, world, rank)
-                    extras["view_sharded"].append(view_sharded_record(
-                        "scannet_fast", args.steps, args.warmup, args.collective, dist, world, rank, dev, peaks,
-                        scenes_per_rank=WORKLOADS["scannet_fast"][1], view_group=(pair, 2)))
+                    extras["view_sharded"].append(guarded(view_sharded_record, "scannet_fast", *common,
+                                                          scenes_per_rank=WORKLOADS["scannet_fast"][1],
+                                                          view_group=(pair, 2)))
 
     if rank == 0:
         cpu = None
