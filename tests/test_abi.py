@@ -63,3 +63,33 @@ def test_cpu_tensors_are_refused():
         ops.backproject(f, pts, P)
     with pytest.raises(_lib.IvxError):
         ops.backproject_scenes(f[None], [(4, 4)], P[None], (2, 2, 2), (1., 1., 1.), [(0., 0., 0.)])
+
+
+def test_3xtf32_entry_points_validate_their_arguments():
+    """ivx_conv3d_ndhwc_f32x3_tc / ivx_split_tf32_ndhwc / the fp32-training variants reject bad calls
+    before anything is launched (host-side checks only: dummy non-NULL pointers are never dereferenced)."""
+    L = _lib.lib()
+    p = _lib.ConvParams()
+    p.batch, p.c_in, p.c_out = 1, 64, 64
+    for d in range(3):
+        p.in_dims[d] = p.out_dims[d] = 8
+        p.kernel[d], p.stride[d], p.pad[d] = 3, 1, 1
+    p.post_scale = 1.0
+    p.in_dtype, p.out_dtype = _lib.IVX_F32, _lib.IVX_F32           # plain fp32 in: not the split format
+    dummy = 1 << 20
+    assert L.ivx_conv3d_ndhwc_f32x3_tc(p, dummy, dummy, None, None, None, dummy, None, 0, None) == -1
+    assert b"IVX_F32X2" in L.ivx_last_error()
+    p.in_dtype = _lib.IVX_F32X2
+    p.c_in = 48                                                    # not a multiple of 32
+    assert L.ivx_conv3d_ndhwc_f32x3_tc(p, dummy, dummy, None, None, None, dummy, None, 0, None) == -2
+    p.c_in = 64
+    assert L.ivx_conv3d_ndhwc_f32x3_tc(p, dummy + 4, dummy, None, None, None, dummy, None, 0, None) == -1
+    assert b"16-byte aligned" in L.ivx_last_error()
+    assert L.ivx_conv3d_ndhwc_f32x3_tc(p, None, dummy, None, None, None, dummy, None, 0, None) == -1
+    assert L.ivx_conv3d_ndhwc_f32x3_tc_view(p, dummy, dummy, None, None, dummy, None, None, 0, None) == -1
+    assert L.ivx_conv3d_wgrad_f32x3_tc(p, None, dummy, dummy, None) == -1
+    assert L.ivx_split_tf32_ndhwc(dummy, dummy, 10, 6, None) == -1  # channels not a multiple of 4
+    assert b"multiple of 4" in L.ivx_last_error()
+    assert L.ivx_split_tf32_ndhwc(None, dummy, 10, 8, None) == -1
+    # the split-K workspace query knows the split format (and needs no GPU)
+    assert L.ivx_conv3d_tc_workspace_bytes(p) >= 0
