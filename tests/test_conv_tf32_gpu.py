@@ -67,7 +67,7 @@ def _bn(cout):
 @pytest.mark.parametrize("variant", ["plain", "bn_relu_res", "res_after_half"])
 def test_tf32_conv(case, variant):
     cin, cout, dims, k, stride, pad, batch = case
-    torch.manual_seed(hash((case, variant)) % 1000)
+    torch.manual_seed(CASES.index(case) * 7 + ["plain", "bn_relu_res", "res_after_half"].index(variant))
     layer = nn.Conv3d(cin, cout, k, stride, pad, bias=(variant != "plain")).to(DEV)
     bn = _bn(cout) if variant != "plain" else None
     relu = variant != "plain"
