@@ -640,7 +640,7 @@ static void plan_tc(const ivx_conv3d_params *p, TcArgs &a) {
     a.x3 = p->in_dtype == IVX_F32X2 ? 1 : 0;
     {
         const char *e = getenv("IVX_X3_DRAIN_STEPS");    // experiments: a huge value = one period per tile
-        a.drain_steps = e ? atoi(e) : 16;
+        a.drain_steps = e ? atoi(e) : 8;
         if (a.drain_steps < 1) a.drain_steps = 1;
     }
     const int k_steps = a.taps[0] * a.taps[1] * a.taps[2] * (p->c_in / (p->in_dtype == IVX_BF16 ? 64 : 32)) *

@@ -466,7 +466,7 @@ static int launch_halo(const ivx_conv3d_params *p, const int perm[3], int mt, co
     a.x3 = X3 ? 1 : 0;
     {
         const char *e = getenv("IVX_X3_DRAIN_GROUPS");   // experiments: a huge value = one period per tile
-        a.drain_groups = e ? atoi(e) : 4;
+        a.drain_groups = e ? atoi(e) : 2;
         if (a.drain_groups < 1) a.drain_groups = 1;
     }
     const int cin_mem = a.x3 ? 2 * p->c_in : p->c_in;    // channels per voxel in memory
